@@ -1,0 +1,202 @@
+// api.cu -- C-ABI of libb2nn.so, part 1: lifecycle, weights, runtime (include/b2nn.h).
+#include <cmath>
+#include <cstring>
+
+#include "comm.hpp"
+#include "common.hpp"
+#include "f64_path.hpp"
+#include "wide_path.hpp"
+
+namespace b2nn {
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char *get_error() { return g_err; }
+}  // namespace b2nn
+
+using namespace b2nn;
+
+extern "C" {
+
+const char *b2nn_last_error(void) { return get_error(); }
+int b2nn_version(void) { return B2NN_VERSION; }
+
+int b2nn_device_count(int32_t *n) {
+    B2_REQUIRE(n != nullptr, B2NN_ERR_INVALID_ARG, "n is null");
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) { cudaGetLastError(); c = 0; }
+    *n = c;
+    return B2NN_OK;
+}
+
+int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t inner_act, double inner_param,
+                int32_t last_act, double last_param, int32_t loss, int32_t precision, int32_t flags, int64_t seed,
+                int32_t device, b2nn_net **out) {
+    B2_REQUIRE(out != nullptr, B2NN_ERR_INVALID_ARG, "out is null");
+    *out = nullptr;
+    B2_REQUIRE(dims != nullptr && n_dims >= 2, B2NN_ERR_INVALID_ARG,
+               "layerDims must hold at least 2 entries (SoftmaxCrossEntropyNeuralNet.java:105)");
+    for (int i = 0; i < n_dims; i++)
+        B2_REQUIRE(dims[i] > 0, B2NN_ERR_INVALID_ARG, "layerDims[%d] = %d must be positive", i, dims[i]);
+    B2_REQUIRE(net_kind == B2NN_NET_SOFTMAX_CE || net_kind == B2NN_NET_GENERAL, B2NN_ERR_INVALID_ARG,
+               "unknown net kind %d", net_kind);
+    B2_REQUIRE(inner_act >= 0 && inner_act <= B2NN_ACT_IDENTITY, B2NN_ERR_INVALID_ARG,
+               "unknown inner activation %d: only the built-in ActivationFunction singletons map to kernels",
+               inner_act);
+    if (net_kind == B2NN_NET_GENERAL) {
+        B2_REQUIRE(last_act >= 0 && last_act <= B2NN_ACT_IDENTITY, B2NN_ERR_INVALID_ARG,
+                   "unknown last activation %d", last_act);
+        B2_REQUIRE(loss == B2NN_LOSS_HALF_SQUARED_ERROR, B2NN_ERR_INVALID_ARG, "unknown loss %d", loss);
+    }
+    B2_REQUIRE(precision == B2NN_PREC_F64 || precision == B2NN_PREC_BF16 || precision == B2NN_PREC_TF32,
+               B2NN_ERR_INVALID_ARG, "unknown precision %d", precision);
+    B2_REQUIRE(precision != B2NN_PREC_TF32, B2NN_ERR_UNSUPPORTED, "TF32 path not implemented yet");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: libb2nn has no CPU fallback");
+        return B2NN_ERR_NO_DEVICE;
+    }
+    if (device < 0) B2_CHECK_CUDA(cudaGetDevice(&device));
+    B2_REQUIRE(device < ndev, B2NN_ERR_INVALID_ARG, "device %d out of range (%d devices)", device, ndev);
+    B2_CHECK_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    B2_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (precision == B2NN_PREC_BF16)
+        B2_REQUIRE(prop.major == 10, B2NN_ERR_UNSUPPORTED,
+                   "the BF16 path is tcgen05 code for sm_100a; device is sm_%d%d", prop.major, prop.minor);
+
+    b2nn_net *net = new b2nn_net();
+    net->device = device;
+    net->n_dims = n_dims;
+    net->dims.assign(dims, dims + n_dims);
+    net->kind = net_kind; net->inner_act = inner_act; net->inner_param = inner_param;
+    net->last_act = last_act; net->last_param = last_param; net->loss = loss;
+    net->precision = precision; net->flags = flags;
+    net->num_sms = prop.multiProcessorCount;
+    net->w_off.resize(n_dims);
+    int64_t tot = 0;
+    for (int l = 0; l + 1 < n_dims; l++) { net->w_off[l] = tot; tot += (int64_t)dims[l] * dims[l + 1]; }
+    net->w_off[n_dims - 1] = tot;
+    net->n_weights = tot;
+
+    // appendLayer (S:139-156): layer-major, row i, col j, W = nextDouble() - 0.5
+    std::vector<double> w((size_t)tot);
+    JavaRandom rng(seed);
+    for (int l = 0; l + 1 < n_dims; l++) {
+        const double sc = (flags & B2NN_FLAG_SCALED_INIT) ? 2.0 * std::sqrt(6.0 / (double)dims[l]) : 1.0;
+        double *W = w.data() + net->w_off[l];
+        const size_t n = (size_t)dims[l] * dims[l + 1];
+        if (flags & B2NN_FLAG_SCALED_INIT)
+            for (size_t q = 0; q < n; q++) W[q] = (rng.next_double() - 0.5) * sc;
+        else
+            for (size_t q = 0; q < n; q++) W[q] = rng.next_double() - 0.5;
+    }
+
+    int st = B2NN_OK;
+    cudaError_t ce = cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking);
+    if (ce != cudaSuccess) {
+        set_error("cudaStreamCreate: %s", cudaGetErrorString(ce));
+        delete net;
+        return B2NN_ERR_CUDA;
+    }
+    net->own_stream = true;
+    st = (precision == B2NN_PREC_F64) ? f64_init(net, w) : wide_init(net, w);
+    if (st != B2NN_OK) {
+        b2nn_destroy(net);
+        return st;
+    }
+    *out = net;
+    return B2NN_OK;
+}
+
+int b2nn_destroy(b2nn_net *net) {
+    if (!net) return B2NN_OK;
+    cudaSetDevice(net->device);
+    cudaDeviceSynchronize();
+    comm_destroy(net);
+    f64_free(net);
+    wide_free(net);
+    if (net->pinned) cudaFreeHost(net->pinned);
+    if (net->dscratch) cudaFree(net->dscratch);
+    if (net->own_stream && net->stream) cudaStreamDestroy(net->stream);
+    delete net;
+    return B2NN_OK;
+}
+
+int b2nn_dims(const b2nn_net *net, int32_t *input_dim, int32_t *output_dim) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    if (input_dim) *input_dim = net->dims[0];                 // getInputDim S:383
+    if (output_dim) *output_dim = net->dims[net->n_dims - 1]; // getOutputDim S:392
+    return B2NN_OK;
+}
+
+int b2nn_num_weights(const b2nn_net *net, int64_t *n) {
+    B2_REQUIRE(net != nullptr && n != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    *n = net->n_weights;
+    return B2NN_OK;
+}
+
+static int xfer_weights(b2nn_net *net, double *w, bool to_host, bool velocity) {
+    B2_REQUIRE(net != nullptr && w != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    if (net->precision == B2NN_PREC_F64) {
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        for (int l = 0; l + 1 < net->n_dims; l++) {
+            const size_t n = (size_t)net->dims[l] * net->dims[l + 1] * sizeof(double);
+            double *dev = velocity ? net->f64[l].v : net->f64[l].w;
+            if (to_host) B2_CHECK_CUDA(cudaMemcpy(w + net->w_off[l], dev, n, cudaMemcpyDeviceToHost));
+            else B2_CHECK_CUDA(cudaMemcpy(dev, w + net->w_off[l], n, cudaMemcpyHostToDevice));
+        }
+        return B2NN_OK;
+    }
+    return to_host ? wide_download_weights(net, w, velocity) : wide_upload_weights(net, w, velocity);
+}
+
+int b2nn_get_weights(b2nn_net *net, double *w) { return xfer_weights(net, w, true, false); }
+int b2nn_set_weights(b2nn_net *net, const double *w) { return xfer_weights(net, const_cast<double *>(w), false, false); }
+int b2nn_get_velocity(b2nn_net *net, double *v) { return xfer_weights(net, v, true, true); }
+int b2nn_set_velocity(b2nn_net *net, const double *v) { return xfer_weights(net, const_cast<double *>(v), false, true); }
+
+int b2nn_sync(b2nn_net *net) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    if (net->aux_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->aux_stream));
+    return B2NN_OK;
+}
+
+int b2nn_set_stream(b2nn_net *net, void *cuda_stream) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    if (net->own_stream && net->stream) cudaStreamDestroy(net->stream);
+    net->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+    net->own_stream = false;
+    return B2NN_OK;
+}
+
+int b2nn_kernel_launches(const b2nn_net *net, int64_t *n) {
+    B2_REQUIRE(net != nullptr && n != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    *n = net->launches;
+    return B2NN_OK;
+}
+
+int b2nn_comm_unique_id(void *id128) {
+    B2_REQUIRE(id128 != nullptr, B2NN_ERR_INVALID_ARG, "id is null");
+    return comm_unique_id(id128);
+}
+
+int b2nn_comm_init(b2nn_net *net, const void *id128, int32_t rank, int32_t world) {
+    B2_REQUIRE(net != nullptr && id128 != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    return comm_init(net, id128, rank, world);
+}
+
+}  // extern "C"

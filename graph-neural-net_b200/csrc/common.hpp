@@ -1,0 +1,154 @@
+// common.hpp -- error plumbing, java.util.Random (for the reference-exact weight init) and the
+// handle structs shared by the FP64 and BF16 paths of libb2nn.so.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/b2nn.h"
+
+namespace b2nn {
+
+// ---- thread-local last error ----------------------------------------------------------------
+void set_error(const char *fmt, ...);
+const char *get_error();
+
+#define B2_CHECK_CUDA(expr)                                                                          \
+    do {                                                                                             \
+        cudaError_t _e = (expr);                                                                     \
+        if (_e != cudaSuccess) {                                                                     \
+            b2nn::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));   \
+            return (_e == cudaErrorMemoryAllocation) ? B2NN_ERR_OOM : B2NN_ERR_CUDA;                 \
+        }                                                                                            \
+    } while (0)
+
+#define B2_REQUIRE(cond, code, ...)            \
+    do {                                       \
+        if (!(cond)) {                         \
+            b2nn::set_error(__VA_ARGS__);      \
+            return (code);                     \
+        }                                      \
+    } while (0)
+
+#define B2_TRY(expr)                 \
+    do {                             \
+        int _s = (expr);             \
+        if (_s != B2NN_OK) return _s;\
+    } while (0)
+
+// ---- java.util.Random: 48-bit LCG fixed by the JDK javadoc.  Product copy used only for the
+// weight init a2 (src/SoftmaxCrossEntropyNeuralNet.java:111,149); the oracle has its own. ------
+struct JavaRandom {
+    uint64_t seed;
+    explicit JavaRandom(int64_t s) : seed(((uint64_t)s ^ 0x5DEECE66DULL) & ((1ULL << 48) - 1)) {}
+    inline int32_t next(int bits) {
+        seed = (seed * 0x5DEECE66DULL + 0xBULL) & ((1ULL << 48) - 1);
+        return (int32_t)(uint32_t)(seed >> (48 - bits));
+    }
+    inline double next_double() {
+        int64_t hi = next(26);
+        int64_t lo = next(27);
+        return (double)((hi << 27) + lo) * 0x1.0p-53;
+    }
+};
+
+inline int pad8(int x) { return (x + 7) & ~7; }
+
+// ---- per-layer state ----------------------------------------------------------------------
+struct F64Layer {
+    double *w = nullptr;  // [in][out] row-major (the boundary layout, src/NeuralNet.java:30-39)
+    double *v = nullptr;  // previousUpdate, same layout
+};
+
+struct WideLayer {
+    int in = 0, out = 0;
+    int ld_n = 0;               // pad8(out): leading dim of [in][out] arrays
+    int ld_t = 0;               // pad8(in):  leading dim of [out][in] arrays
+    float *w = nullptr;         // FP32 master [in][ld_n]
+    float *v = nullptr;         // FP32 velocity [in][ld_n]
+    float *g = nullptr;         // FP32 gradient [in][ld_n] (data-parallel only)
+    __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]  : B operand of the delta GEMM (N=in, K=out)
+    __nv_bfloat16 *wt = nullptr;  // BF16 [out][ld_t] : B operand of the forward GEMM (N=out, K=in)
+    CUtensorMap tm_wt, tm_wn;     // B-operand maps (box 256 x 64)
+};
+
+// activations / deltas for one batch size
+struct WideBatch {
+    int B = 0, ldB = 0;
+    std::vector<__nv_bfloat16 *> a;    // a[l]  [B][pad8(d_l)]   l = 0..L-1 (activations incl. f(x))
+    std::vector<__nv_bfloat16 *> at;   // at[l] [d_l][ldB]
+    std::vector<__nv_bfloat16 *> d;    // d[l]  [B][pad8(d_l)]   l = 1..L   (deltas)
+    std::vector<__nv_bfloat16 *> dt;   // dt[l] [d_l][ldB]
+    float *logits = nullptr;           // [B][pad8(d_L)] FP32
+    float *row_loss = nullptr;         // [B]
+    int32_t *labels = nullptr;         // [B]
+    float *tdense = nullptr;           // [B][pad8(d_L)] FP32 dense targets (optional path)
+    void *xstage = nullptr;            // staged raw input rows [B][d0] (any dtype, 8 B / element max)
+    std::vector<CUtensorMap> tm_a, tm_at, tm_d, tm_dt;  // A-operand maps (box 128 x 64)
+    double *loss_sum = nullptr;        // device scalar(s)
+};
+
+}  // namespace b2nn
+
+struct b2nn_dataset {
+    b2nn_net *net = nullptr;
+    int64_t n = 0;
+    int d0 = 0, dL = 0;
+    int location = 0;
+    int x_dtype = 0;          // dtype rows are stored in (F64 for F64 nets; as given otherwise)
+    void *x = nullptr;        // device rows [n][d0], or pinned host rows (mapped) for HOST_PINNED
+    void *x_dev_alias = nullptr;  // device-visible pointer to x
+    double *t = nullptr;      // device dense targets [n][dL] (F64) or null
+    int32_t *labels = nullptr;  // device labels [n] or null (one-hot targets implied)
+    int32_t *labels_eval = nullptr;  // labels used for hit counting: == labels, or derived from t (M:183-186)
+};
+
+struct b2nn_net {
+    int device = 0;
+    int n_dims = 0;
+    std::vector<int> dims;
+    int kind = 0, inner_act = 0, last_act = 0, loss = 0, precision = 0, flags = 0;
+    double inner_param = 0, last_param = 0;
+    int64_t n_weights = 0;
+    std::vector<int64_t> w_off;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaStream_t aux_stream = nullptr;  // copies / collectives
+    int num_sms = 0;
+    int64_t launches = 0;
+
+    // FP64 path
+    std::vector<b2nn::F64Layer> f64;
+    struct F64Work {
+        int cap_rows = 0;
+        std::vector<double *> z, a, d;  // per layer [rows][d_l]
+        double *t = nullptr;            // [rows][dL]
+        double *row_loss = nullptr;     // [rows]
+        int32_t *pred = nullptr;        // [rows]
+        int32_t *idx = nullptr;
+        double *xin = nullptr;          // staged input rows
+    } fw;
+    double *f64_grad = nullptr;  // [P] scratch for weight_gradient
+
+    // BF16 path
+    std::vector<b2nn::WideLayer> wide;
+    b2nn::WideBatch wb;
+
+    // data-parallel
+    void *nccl_comm = nullptr;
+    int rank = 0, world = 1;
+    std::vector<cudaEvent_t> layer_events;
+    cudaEvent_t comm_done = nullptr;
+
+    // host staging
+    void *pinned = nullptr;
+    size_t pinned_bytes = 0;
+    void *dscratch = nullptr;
+    size_t dscratch_bytes = 0;
+};

@@ -1,0 +1,339 @@
+// wide_path.cu -- host orchestration of the BF16 tensor-core path: per-step sequence of
+// tcgen05 GEMMs (gemm_tcgen05.cuh) and the HBM-bound kernels around them (wide_kernels.cuh).
+// Data layout in HBM (per layer l with W_l: d_l x d_{l+1}):
+//   w, v   FP32 [d_l][pad8(d_{l+1})]           master weights / velocity (boundary layout, padded)
+//   wn     BF16 [d_l][pad8(d_{l+1})]           K-major B operand of the delta GEMM
+//   wt     BF16 [d_{l+1}][pad8(d_l)]           K-major B operand of the forward GEMM
+//   a[l]   BF16 [B][pad8(d_l)], at[l] [d_l][pad8(B)]     activations (+ transposed for the gradient GEMM)
+//   d[l]   BF16 [B][pad8(d_l)], dt[l] [d_l][pad8(B)]     deltas      (+ transposed)
+#include "wide_path.hpp"
+
+#include "comm.hpp"
+#include "gemm_tcgen05.cuh"
+#include "wide_kernels.cuh"
+
+namespace b2nn {
+
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                        const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+
+static PFN_tmapEncodeTiled get_encode_fn() {
+    static PFN_tmapEncodeTiled fn = nullptr;
+    if (fn) return fn;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = reinterpret_cast<PFN_tmapEncodeTiled>(p);
+    return fn;
+}
+
+// K-major BF16 operand: global [rows][ld] with `k` valid elements per row; box = box_rows x 64,
+// 128-byte swizzle (matches make_desc_kmajor_sw128), out-of-bounds elements read as zero.
+int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t k, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+    PFN_tmapEncodeTiled fn = get_encode_fn();
+    B2_REQUIRE(fn != nullptr, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t gdim[2] = {k, rows};
+    cuuint64_t gstride[1] = {ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B2_REQUIRE(r == CUDA_SUCCESS, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (k=%llu rows=%llu ld=%llu)",
+               (int)r, (unsigned long long)k, (unsigned long long)rows, (unsigned long long)ld);
+    return B2NN_OK;
+}
+
+template <int EPI>
+static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           GEMM_SMEM_BYTES));
+        attr_done = true;
+    }
+    const int tiles = ((g.M + GEMM_BM - 1) / GEMM_BM) * ((g.N + GEMM_BN - 1) / GEMM_BN);
+    const int grid = tiles < net->num_sms ? tiles : net->num_sms;
+    gemm_tn_bf16_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+int wide_gemm_raw(b2nn_net *net, int epi, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+    switch (epi) {
+    case EPI_ACT: return launch_gemm<EPI_ACT>(net, ta, tb, g);
+    case EPI_LOGITS: return launch_gemm<EPI_LOGITS>(net, ta, tb, g);
+    case EPI_DX: return launch_gemm<EPI_DX>(net, ta, tb, g);
+    case EPI_DW_UPDATE: return launch_gemm<EPI_DW_UPDATE>(net, ta, tb, g);
+    default: return launch_gemm<EPI_DW_STORE>(net, ta, tb, g);
+    }
+}
+
+static int rebuild_bf16_copies(b2nn_net *net, int l) {
+    WideLayer &y = net->wide[l];
+    dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
+    wide::sgd_update<<<grid, block, 0, net->stream>>>(nullptr, y.w, y.v, y.in, y.out, y.ld_n, 0.f, 0.f, 1, y.wn,
+                                                       y.wt, y.ld_t);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity) {
+    const int L = net->n_dims - 1;
+    for (int l = 0; l < L; l++) {
+        WideLayer &y = net->wide[l];
+        std::vector<float> tmp((size_t)y.in * y.ld_n, 0.f);
+        const double *src = w_flat + net->w_off[l];
+        for (int i = 0; i < y.in; i++)
+            for (int j = 0; j < y.out; j++) tmp[(size_t)i * y.ld_n + j] = (float)src[(size_t)i * y.out + j];
+        B2_CHECK_CUDA(cudaMemcpyAsync(velocity ? y.v : y.w, tmp.data(), tmp.size() * sizeof(float),
+                                      cudaMemcpyHostToDevice, net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        if (!velocity) B2_TRY(rebuild_bf16_copies(net, l));
+    }
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    return B2NN_OK;
+}
+
+int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity) {
+    const int L = net->n_dims - 1;
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    if (net->aux_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->aux_stream));
+    for (int l = 0; l < L; l++) {
+        WideLayer &y = net->wide[l];
+        std::vector<float> tmp((size_t)y.in * y.ld_n);
+        B2_CHECK_CUDA(cudaMemcpy(tmp.data(), velocity ? y.v : y.w, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        double *dst = w_flat + net->w_off[l];
+        for (int i = 0; i < y.in; i++)
+            for (int j = 0; j < y.out; j++) dst[(size_t)i * y.out + j] = (double)tmp[(size_t)i * y.ld_n + j];
+    }
+    return B2NN_OK;
+}
+
+int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
+    const int L = net->n_dims - 1;
+    net->wide.resize(L);
+    for (int l = 0; l < L; l++) {
+        WideLayer &y = net->wide[l];
+        y.in = net->dims[l]; y.out = net->dims[l + 1];
+        y.ld_n = pad8(y.out); y.ld_t = pad8(y.in);
+        const size_t nf = (size_t)y.in * y.ld_n;
+        B2_CHECK_CUDA(cudaMalloc(&y.w, nf * sizeof(float)));
+        B2_CHECK_CUDA(cudaMalloc(&y.v, nf * sizeof(float)));
+        B2_CHECK_CUDA(cudaMemset(y.v, 0, nf * sizeof(float)));
+        B2_CHECK_CUDA(cudaMalloc(&y.wn, nf * sizeof(__nv_bfloat16)));
+        B2_CHECK_CUDA(cudaMalloc(&y.wt, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
+        B2_CHECK_CUDA(cudaMemset(y.wn, 0, nf * sizeof(__nv_bfloat16)));
+        B2_CHECK_CUDA(cudaMemset(y.wt, 0, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
+        B2_TRY(make_tmap_bf16(&y.tm_wt, y.wt, y.in, y.out, y.ld_t, GEMM_BN));  // forward: N=out, K=in
+        B2_TRY(make_tmap_bf16(&y.tm_wn, y.wn, y.out, y.in, y.ld_n, GEMM_BN));  // delta:   N=in,  K=out
+    }
+    return wide_upload_weights(net, w_host.data(), false);
+}
+
+static void free_batch(b2nn_net *net) {
+    WideBatch &b = net->wb;
+    for (auto p : b.a) cudaFree(p);
+    for (auto p : b.at) cudaFree(p);
+    for (auto p : b.d) cudaFree(p);
+    for (auto p : b.dt) cudaFree(p);
+    b.a.clear(); b.at.clear(); b.d.clear(); b.dt.clear();
+    cudaFree(b.logits); cudaFree(b.row_loss); cudaFree(b.labels); cudaFree(b.tdense); cudaFree(b.xstage);
+    cudaFree(b.loss_sum);
+    b.logits = nullptr; b.row_loss = nullptr; b.labels = nullptr; b.tdense = nullptr; b.xstage = nullptr;
+    b.loss_sum = nullptr;
+    b.B = 0;
+}
+
+void wide_free(b2nn_net *net) {
+    free_batch(net);
+    for (auto &y : net->wide) { cudaFree(y.w); cudaFree(y.v); cudaFree(y.g); cudaFree(y.wn); cudaFree(y.wt); }
+    net->wide.clear();
+}
+
+int wide_ensure_batch(b2nn_net *net, int B) {
+    WideBatch &b = net->wb;
+    if (b.B == B) return B2NN_OK;
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    free_batch(net);
+    const int nd = net->n_dims, L = nd - 1;
+    b.ldB = pad8(B);
+    b.a.assign(nd, nullptr); b.at.assign(nd, nullptr); b.d.assign(nd, nullptr); b.dt.assign(nd, nullptr);
+    b.tm_a.resize(nd); b.tm_at.resize(nd); b.tm_d.resize(nd); b.tm_dt.resize(nd);
+    for (int l = 0; l < nd; l++) {
+        const int dl = net->dims[l], ld = pad8(dl);
+        if (l < L) {
+            B2_CHECK_CUDA(cudaMalloc(&b.a[l], (size_t)B * ld * 2));
+            B2_CHECK_CUDA(cudaMalloc(&b.at[l], (size_t)dl * b.ldB * 2));
+            B2_CHECK_CUDA(cudaMemset(b.at[l], 0, (size_t)dl * b.ldB * 2));
+            B2_TRY(make_tmap_bf16(&b.tm_a[l], b.a[l], dl, B, ld, GEMM_BM));       // forward A: M=B, K=d_l
+            B2_TRY(make_tmap_bf16(&b.tm_at[l], b.at[l], B, dl, b.ldB, GEMM_BM));  // gradient A: M=d_l, K=B
+        }
+        if (l >= 1) {
+            B2_CHECK_CUDA(cudaMalloc(&b.d[l], (size_t)B * ld * 2));
+            B2_CHECK_CUDA(cudaMalloc(&b.dt[l], (size_t)dl * b.ldB * 2));
+            B2_CHECK_CUDA(cudaMemset(b.dt[l], 0, (size_t)dl * b.ldB * 2));
+            B2_TRY(make_tmap_bf16(&b.tm_d[l], b.d[l], dl, B, ld, GEMM_BM));       // delta A: M=B, K=d_l
+            B2_TRY(make_tmap_bf16(&b.tm_dt[l], b.dt[l], B, dl, b.ldB, GEMM_BN));  // gradient B: N=d_l, K=B
+        }
+    }
+    const int ldL = pad8(net->dims[L]);
+    B2_CHECK_CUDA(cudaMalloc(&b.logits, (size_t)B * ldL * sizeof(float)));
+    B2_CHECK_CUDA(cudaMalloc(&b.row_loss, (size_t)B * sizeof(float)));
+    B2_CHECK_CUDA(cudaMalloc(&b.labels, (size_t)B * sizeof(int32_t)));
+    B2_CHECK_CUDA(cudaMalloc(&b.tdense, (size_t)B * ldL * sizeof(float)));
+    B2_CHECK_CUDA(cudaMalloc(&b.xstage, (size_t)B * net->dims[0] * sizeof(double)));
+    B2_CHECK_CUDA(cudaMalloc(&b.loss_sum, 2 * sizeof(double)));
+    b.B = B;
+    return B2NN_OK;
+}
+
+// K8: a0 = f(X[idx]) as BF16 (+ transposed).  X device-visible in dtype x_dtype.
+int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st) {
+    WideBatch &b = net->wb;
+    const int d0 = net->dims[0];
+    dim3 grid((d0 + 31) / 32, (B + 31) / 32), block(32, 8);
+    const float p = (float)net->inner_param;
+    switch (x_dtype) {
+    case B2NN_DT_F64:
+        wide::input_prologue<double><<<grid, block, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p,
+                                                            b.a[0], pad8(d0), b.at[0], b.ldB);
+        break;
+    case B2NN_DT_F32:
+        wide::input_prologue<float><<<grid, block, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p,
+                                                           b.a[0], pad8(d0), b.at[0], b.ldB);
+        break;
+    case B2NN_DT_BF16:
+        wide::input_prologue<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
+                                                                   net->inner_act, p, b.a[0], pad8(d0), b.at[0],
+                                                                   b.ldB);
+        break;
+    default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
+    }
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+// forward GEMMs (replaces S:169-193); the last one keeps FP32 logits
+int wide_forward(b2nn_net *net, int B) {
+    WideBatch &b = net->wb;
+    const int L = net->n_dims - 1;
+    for (int l = 0; l < L; l++) {
+        WideLayer &y = net->wide[l];
+        GemmArgs g{};
+        g.M = B; g.N = y.out; g.K = y.in;
+        g.act = net->inner_act; g.act_param = (float)net->inner_param;
+        if (l + 1 < L) {
+            g.out0 = b.a[l + 1]; g.ld0 = pad8(y.out);
+            g.out1 = b.at[l + 1]; g.ld1 = b.ldB;
+            B2_TRY(launch_gemm<EPI_ACT>(net, b.tm_a[l], y.tm_wt, g));
+        } else {
+            g.out0 = b.logits; g.ld0 = pad8(y.out);
+            B2_TRY(launch_gemm<EPI_LOGITS>(net, b.tm_a[l], y.tm_wt, g));
+        }
+    }
+    return B2NN_OK;
+}
+
+// K5/K6: output delta + per-row loss
+int wide_output(b2nn_net *net, int B, bool dense_targets) {
+    WideBatch &b = net->wb;
+    const int L = net->n_dims - 1, dL = net->dims[L], ldL = pad8(dL);
+    wide::output_delta<<<(B + 31) / 32, 256, 0, net->stream>>>(
+        b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
+        net->last_act, (float)net->last_param, b.d[L], ldL, b.dt[L], b.ldB, b.row_loss);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+// backward: deltas (S:260-278), gradient GEMMs with the batch sum as the K dimension (S:279-283 +
+// S:305-322) and the momentum update (S:325-342) -- fused into the gradient GEMM's epilogue on one
+// GPU; all-reduced per layer on a side stream and then updated (K7) when data-parallel.
+int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
+    WideBatch &b = net->wb;
+    const int L = net->n_dims - 1;
+    const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
+    for (int l = L - 1; l >= 0; l--) {
+        WideLayer &y = net->wide[l];
+        if (l >= 1) {
+            GemmArgs g{};
+            g.M = B; g.N = y.in; g.K = y.out;
+            g.out0 = b.d[l]; g.ld0 = pad8(y.in);
+            g.out1 = b.dt[l]; g.ld1 = b.ldB;
+            g.aux = b.a[l]; g.ldaux = pad8(y.in);
+            g.act = net->inner_act; g.act_param = (float)net->inner_param;
+            B2_TRY(launch_gemm<EPI_DX>(net, b.tm_d[l + 1], y.tm_wn, g));
+        }
+        GemmArgs g{};
+        g.M = y.in; g.N = y.out; g.K = B;
+        g.ldw = y.ld_n;
+        if (net->world == 1) {
+            g.w = y.w; g.v = y.v;
+            g.out0 = y.wn; g.ld0 = y.ld_n;
+            g.out1 = y.wt; g.ld1 = y.ld_t;
+            g.scale = scale; g.momentum = (float)momentum;
+            B2_TRY(launch_gemm<EPI_DW_UPDATE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+        } else {
+            g.w = y.g;
+            B2_TRY(launch_gemm<EPI_DW_STORE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+            B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
+            B2_CHECK_CUDA(cudaStreamWaitEvent(net->aux_stream, net->layer_events[l], 0));
+            B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, net->aux_stream));
+            dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
+            wide::sgd_update<<<grid, block, 0, net->aux_stream>>>(y.g, y.w, y.v, y.in, y.out, y.ld_n, scale,
+                                                                  (float)momentum, 0, y.wn, y.wt, y.ld_t);
+            net->launches++;
+            B2_CHECK_CUDA(cudaGetLastError());
+        }
+    }
+    if (net->world > 1) {
+        B2_CHECK_CUDA(cudaEventRecord(net->comm_done, net->aux_stream));
+        B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->comm_done, 0));
+    }
+    return B2NN_OK;
+}
+
+int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss) {
+    WideBatch &b = net->wb;
+    const int L = net->n_dims - 1, dL = net->dims[L];
+    wide::eval_rows<<<(rows + 7) / 8, 256, 0, net->stream>>>(b.logits, pad8(dL), labels_dev, rows, dL, net->kind,
+                                                             net->last_act, (float)net->last_param, pred_dev,
+                                                             want_loss ? b.row_loss : nullptr);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,
+                long long *hits_dev) {
+    wide::reduce_rows<<<1, 256, 0, net->stream>>>(loss_sum_dev ? net->wb.row_loss : nullptr, pred_dev, labels_dev,
+                                                  rows, loss_sum_dev, hits_dev);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B) {
+    wide::gather_labels<<<(B + 255) / 256, 256, 0, net->stream>>>(labels, idx_dev, B, net->wb.labels);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+int wide_gather_targets(b2nn_net *net, const double *T, const int32_t *idx_dev, int B) {
+    const int dL = net->dims[net->n_dims - 1];
+    wide::gather_targets<<<B, 128, 0, net->stream>>>(T, idx_dev, B, dL, net->wb.tdense, pad8(dL));
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+}  // namespace b2nn

@@ -1,0 +1,23 @@
+// wide_path.hpp -- BF16 tensor-core path entry points (see wide_path.cu)
+#pragma once
+#include "common.hpp"
+
+namespace b2nn {
+struct GemmArgs;
+int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t k, uint64_t rows, uint64_t ld, uint32_t box_rows);
+int wide_gemm_raw(b2nn_net *net, int epi, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g);
+int wide_init(b2nn_net *net, const std::vector<double> &w_host);
+void wide_free(b2nn_net *net);
+int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity);
+int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity);
+int wide_ensure_batch(b2nn_net *net, int B);
+int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st);
+int wide_forward(b2nn_net *net, int B);
+int wide_output(b2nn_net *net, int B, bool dense_targets);
+int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum);
+int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss);
+int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,
+                long long *hits_dev);
+int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B);
+int wide_gather_targets(b2nn_net *net, const double *T, const int32_t *idx_dev, int B);
+}  // namespace b2nn

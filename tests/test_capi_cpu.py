@@ -1,0 +1,110 @@
+"""CPU-side tests of the boundary: libb2nn.so loads without a GPU, exports every symbol
+include/b2nn.h declares, reports NO_DEVICE instead of falling back to a CPU path, and the host
+logic above the C-ABI (function singletons, sampler, MNIST harness pieces) behaves like the
+reference's.  No compute call is made here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "b2nn.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2nn_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported(g):
+    names = _declared_symbols()
+    assert len(names) >= 25
+    lib = C.CDLL(g.capi.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), "libb2nn.so does not export %s" % n
+    # and the Python binding covers exactly the header
+    assert sorted(g.capi.SIGNATURES) == names
+
+
+def test_version_and_error_text(g):
+    assert g.capi.lib().b2nn_version() == 100
+    assert isinstance(g.capi.lib().b2nn_last_error(), bytes)
+
+
+def test_no_cpu_fallback_without_device(g):
+    if g.capi.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(g.capi.B2nnError) as e:
+        g.SoftmaxCrossEntropyNeuralNet([4, 3, 2], g.LEAKY_RELU, g.LEAKY_RELU_PRIME)
+    assert e.value.code == g.capi.ERR_NO_DEVICE
+    assert "no CPU fallback" in str(e.value)
+
+
+def test_constructor_argument_errors(g):
+    # argument validation happens before any device is touched
+    with pytest.raises(ValueError):
+        g.SoftmaxCrossEntropyNeuralNet([4], g.LEAKY_RELU, g.LEAKY_RELU_PRIME)          # S:105
+    with pytest.raises(ValueError):
+        g.SoftmaxCrossEntropyNeuralNet([4, 0, 2], g.LEAKY_RELU, g.LEAKY_RELU_PRIME)    # S:141
+    with pytest.raises(ValueError):
+        g.SoftmaxCrossEntropyNeuralNet([4, 2], None, g.LEAKY_RELU_PRIME)               # S:106
+    with pytest.raises(ValueError):                                                   # arbitrary lambda: no kernel
+        g.SoftmaxCrossEntropyNeuralNet([4, 2], lambda a: a, lambda a: 1.0)
+    with pytest.raises(ValueError):                                                   # mismatched pair
+        g.SoftmaxCrossEntropyNeuralNet([4, 2], g.LEAKY_RELU, g.SIGMOID_PRIME)
+    with pytest.raises(ValueError):
+        g.GeneralNeuralNet([4, 2], g.SIGMOID, g.SIGMOID_PRIME, g.SIGMOID, g.SIGMOID_PRIME,
+                           lambda c, e: 0.0, lambda c, e: 0.0)
+    with pytest.raises(NotImplementedError):                                          # TF32 reserved
+        g.SoftmaxCrossEntropyNeuralNet([4, 2], g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_TF32)
+
+
+def test_function_singletons_match_oracle_scalars(g, orc):
+    zs = [-3.0, -0.5, 0.0, 1e-9, 0.7, 4.0]
+    pairs = [("leaky_relu", 0, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, 0.01), ("sigmoid", 1, g.SIGMOID, g.SIGMOID_PRIME, 0.0),
+             ("relu", 2, g.RELU, g.RELU_PRIME, 0.0), ("tanh", 3, g.TANH, g.TANH_PRIME, 0.0),
+             ("identity", 4, g.IDENTITY, g.IDENTITY_PRIME, 0.0)]
+    for name, kid, f, fp, p in pairs:
+        assert f.kernel_id == kid == orc.ACT[name] and fp.kernel_id == kid
+        for z in zs:
+            assert abs(f.func(z) - orc.lib().orc_act(kid, p, z)) <= 1e-15
+            assert abs(fp.func(z) - orc.lib().orc_act_prime(kid, p, z)) <= 1e-15
+    assert g.HALF_SQUARED_ERROR.loss(0.8, 1.0) == orc.lib().orc_loss(0, 0.8, 1.0)
+    assert g.HALF_SQUARED_ERROR_PRIME.func(0.8, 1.0) == orc.lib().orc_loss_prime(0, 0.8, 1.0)
+    # the in-tree lambdas (MNISTTrainer.java:234-235)
+    assert g.LEAKY_RELU.func(-2.0) == 0.01 * -2.0 and g.LEAKY_RELU_PRIME.func(0.0) == 0.01
+
+
+@pytest.mark.parametrize("n,B,iters", [(60000, 16, 7600), (100, 7, 40), (17, 16, 9)])
+def test_native_sampler_matches_oracle(g, orc, n, B, iters):
+    got = g.Sampler(n, seed=1).draw(iters, B)
+    s = orc.Sampler(n, seed=1)
+    ref = np.stack([s.sample(B) for _ in range(iters)])
+    assert (got == ref).all()
+
+
+def test_sampler_argument_errors(g):
+    with pytest.raises(ValueError):
+        g.Sampler(0)
+    with pytest.raises(ValueError):
+        g.Sampler(10).draw(1, 10)   # batchSize < rows is strict (T:63, Q17)
+
+
+def test_log_row_and_idx_readers_match_oracle(g, orc, golden_dir, tmp_path):
+    from gnn_b200 import mnist
+    row = mnist.MNISTTrainer.formatLogRow([784, 300, 100, 10], 100000, 0.0125, 16, 0.9, False, 0.99973, 0.978)
+    assert row == orc.format_log_row([784, 300, 100, 10], 100000, 0.0125, 16, 0.9, False, 0.99973, 0.978)
+    assert row == open(os.path.join(golden_dir, "trainLog_reference.csv")).read().splitlines()[3] + "\n"
+    lp = os.path.join(golden_dir, "mnist", "t10k-labels-idx1-ubyte")
+    assert (mnist.read_idx_labels(lp) == orc.read_idx_labels(lp)).all()
+    ip = str(tmp_path / "img")
+    mnist.write_surrogate_images(mnist.read_idx_labels(lp)[:50], ip, seed=2)
+    a, b = mnist.read_idx_images(ip), orc.read_idx_images(ip)
+    assert a.shape == (50, 784) and (a == b).all() and a.min() >= 0.0 and a.max() <= 1.0
+    ip2 = str(tmp_path / "img2")
+    mnist.write_surrogate_images(mnist.read_idx_labels(lp)[:50], ip2, seed=2)
+    assert open(ip, "rb").read() == open(ip2, "rb").read()   # deterministic
+    oh = mnist.one_hot(np.array([3, 0, 9]))
+    assert oh.shape == (3, 10) and oh[0, 3] == 1 and oh.sum() == 3

@@ -1,0 +1,57 @@
+"""End-to-end MNISTTrainer path on the GPU (FP64 parity mode) against the oracle run on the same
+data in the same order: IDX parse -> /255.0 -> train with the Random(1) sampler -> `>=` argmax
+accuracy over both partitions -> trainLog.csv row.  The image files are the deterministic
+MNIST-shaped SURROGATE (the reference mount lacks the real image files); the labels are the
+reference's real label files (tests/golden/mnist)."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def data_dir(tmp_path_factory, golden_dir):
+    from gnn_b200 import mnist
+    d = tmp_path_factory.mktemp("mnist_data")
+    # small slices of the real label files keep the CPU oracle leg short
+    for lab, img, n, seed in (("train-labels-idx1-ubyte", "train-images-idx3-ubyte", 3000, 1),
+                              ("t10k-labels-idx1-ubyte", "t10k-images-idx3-ubyte", 1000, 2)):
+        labels = mnist.read_idx_labels(os.path.join(golden_dir, "mnist", lab))[:n]
+        import struct
+        with open(d / lab, "wb") as f:
+            f.write(struct.pack(">ii", 2049, n))
+            f.write(labels.astype(np.uint8).tobytes())
+        mnist.write_surrogate_images(labels, str(d / img), seed)
+    return str(d)
+
+
+@pytest.mark.parametrize("dims,B,step", [([784, 100, 50, 10], 8, 0.01), ([784, 300, 100, 10], 16, 0.0125)])
+def test_mnist_trainer_matches_oracle(g, orc, data_dir, tmp_path, dims, B, step):
+    from gnn_b200 import mnist
+    iters = 400
+    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME)   # reference init, undamped
+    tr = g.MNISTTrainer(net, data_dir, str(tmp_path / "logs"))
+    tr.train(iters, step, B, 0.9, False, False, False)
+    train_acc, test_acc = tr.testOnTrainingData(), tr.testOnTestData()
+    tr.logTest(dims, iters, step, B, 0.9, False, train_acc, test_acc)
+
+    xtr = orc.read_idx_images(os.path.join(data_dir, "train-images-idx3-ubyte"))
+    ltr = orc.read_idx_labels(os.path.join(data_dir, "train-labels-idx1-ubyte"))
+    xte = orc.read_idx_images(os.path.join(data_dir, "t10k-images-idx3-ubyte"))
+    lte = orc.read_idx_labels(os.path.join(data_dir, "t10k-labels-idx1-ubyte"))
+    ref = orc.OracleNet(dims)
+    ref.train(xtr, mnist.one_hot(ltr), iters, B, step, 0.9)
+    rh_tr, rp_tr = ref.evaluate(xtr, ltr)
+    rh_te, rp_te = ref.evaluate(xte, lte)
+
+    wr = ref.get_weights()
+    assert np.max(np.abs(net.getWeights() - wr) / np.maximum(1e-3, np.abs(wr))) <= 1e-9
+    _, _, p_te = tr.testingPartition.evaluate(want_pred=True)
+    _, _, p_tr = tr.trainer.dataMaster.evaluate(want_pred=True)
+    assert (p_te == rp_te).all() and (p_tr == rp_tr).all()          # bit-exact argmax predictions
+    assert train_acc == rh_tr / len(ltr) and test_acc == rh_te / len(lte)
+    assert test_acc > 0.5                                            # it actually learned the surrogate
+    row = open(tmp_path / "logs" / "trainLog.csv").read()
+    assert row == orc.format_log_row(dims, iters, step, B, 0.9, False, rh_tr / len(ltr), rh_te / len(lte))

@@ -1,0 +1,165 @@
+"""GPU tests of the BF16 tcgen05 path through the C-ABI, against the FP64 CPU oracle.
+
+Tolerances (stated here): BF16 operands (8-bit mantissa) with FP32 accumulation --
+  - plain contraction y = x W (identity activations): |diff| <= 2e-2 * max|y|;
+  - one-step update direction: relative Frobenius error <= 3e-2; batch loss within 2e-2 relative;
+  - loss curve over the first 40 steps within 5 % of the oracle's.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_round(a):
+    """round-to-nearest-even to bfloat16, returned as float64"""
+    a32 = np.ascontiguousarray(a, dtype=np.float32)
+    u = a32.view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32).astype(np.float64)
+
+
+def wide_net(g, dims, **kw):
+    flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX
+    return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+                                          flags=flags, **kw)
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 256), (256, 512, 512), (100, 200, 1000), (4096, 1000, 136),
+                                    (37, 8, 8), (300, 4096, 264)])
+def test_gemm_forward_identity(g, M, K, N):
+    """GeneralNeuralNet with identity activations makes propagate() the bare tcgen05 contraction
+    y = x W: exercises TMA zero-fill on ragged M/N/K, the UMMA descriptors and the TMEM epilogue."""
+    net = g.GeneralNeuralNet([K, N], g.IDENTITY, g.IDENTITY_PRIME, g.IDENTITY, g.IDENTITY_PRIME,
+                             g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, precision=g.capi.PREC_BF16)
+    rng = np.random.RandomState(M + K + N)
+    W = rng.randn(K, N) * 0.5
+    net.setWeights(W.ravel())
+    x = rng.randn(M, K)
+    y = net.propagate(x)
+    ref = bf16_round(x) @ bf16_round(W)          # exact operands, FP64 accumulate
+    err = np.abs(y - ref).max()
+    assert err <= 1e-3 * max(1.0, np.abs(ref).max()), (err, np.abs(ref).max())
+
+
+def test_gemm_two_layer_chain(g):
+    """two chained contractions: the first epilogue stores BF16 activations that feed the second"""
+    K, H, N, M = 320, 520, 72, 260
+    net = g.GeneralNeuralNet([K, H, N], g.IDENTITY, g.IDENTITY_PRIME, g.IDENTITY, g.IDENTITY_PRIME,
+                             g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, precision=g.capi.PREC_BF16)
+    rng = np.random.RandomState(9)
+    W0, W1 = rng.randn(K, H) * 0.1, rng.randn(H, N) * 0.1
+    net.setWeights(np.concatenate([W0.ravel(), W1.ravel()]))
+    x = rng.randn(M, K)
+    h = bf16_round(bf16_round(x) @ bf16_round(W0))
+    ref = h @ bf16_round(W1)
+    y = net.propagate(x)
+    assert np.abs(y - ref).max() <= 2e-2 * np.abs(ref).max()
+
+
+def test_weights_roundtrip_and_init(g, orc):
+    dims = [64, 40, 24]
+    net = wide_net(g, dims)
+    ref = orc.OracleNet(dims)
+    w = net.getWeights()
+    r = ref.get_weights()
+    # scaled init: (U[-0.5,0.5) from the same LCG stream) * 2*sqrt(6/fan_in), stored as FP32
+    sc = np.concatenate([np.full(64 * 40, 2 * np.sqrt(6 / 64)), np.full(40 * 24, 2 * np.sqrt(6 / 40))])
+    assert np.allclose(w, (r * sc).astype(np.float32), rtol=0, atol=0)
+    v = np.linspace(-1, 1, net.numWeights)
+    net.setWeights(v)
+    assert np.array_equal(net.getWeights(), v.astype(np.float32).astype(np.float64))
+
+
+@pytest.mark.parametrize("dims,B", [([512, 384, 256, 100], 256), ([784, 300, 100, 10], 64),
+                                     ([1000, 520, 1000], 136)])
+def test_one_step_vs_oracle(g, orc, dims, B):
+    net = wide_net(g, dims)
+    ref = orc.OracleNet(dims)
+    ref.set_weights(net.getWeights())
+    rng = np.random.RandomState(1)
+    x = rng.rand(B, dims[0])
+    lab = rng.randint(0, dims[-1], B).astype(np.int32)
+    t = np.zeros((B, dims[-1]))
+    t[np.arange(B), lab] = 1.0
+    w0 = ref.get_weights()
+    ref_loss = np.mean([ref.loss(x[i], t[i]) for i in range(B)])
+    loss = net.gradientStepLabeled(x.astype(np.float32), lab, 0.05, 0.9, returnLoss=True)
+    ref.gradient_step(x, t, 0.05, 0.9)
+    assert abs(loss - ref_loss) <= 2e-2 * max(1.0, abs(ref_loss))
+    du, du_ref = net.getWeights() - w0, ref.get_weights() - w0
+    # per layer, so a wrong small layer cannot hide behind a big one
+    off = 0
+    for l in range(len(dims) - 1):
+        n = dims[l] * dims[l + 1]
+        rel = np.linalg.norm(du[off:off + n] - du_ref[off:off + n]) / np.linalg.norm(du_ref[off:off + n])
+        assert rel <= 3e-2, (l, rel)
+        off += n
+    assert np.linalg.norm(net.getVelocity() - ref.get_velocity()) <= 3e-2 * np.linalg.norm(ref.get_velocity())
+
+
+def test_dense_target_step_matches_labeled(g):
+    dims, B = [256, 128, 32], 64
+    a, b = wide_net(g, dims), wide_net(g, dims)
+    rng = np.random.RandomState(2)
+    x = rng.rand(B, 256)
+    lab = rng.randint(0, 32, B).astype(np.int32)
+    t = np.zeros((B, 32))
+    t[np.arange(B), lab] = 1.0
+    la = a.gradientStep((x, t), 0.05, 0.9, returnLoss=True)       # drop-in double path
+    lb = b.gradientStepLabeled(x, lab, 0.05, 0.9, returnLoss=True)
+    assert abs(la - lb) <= 1e-6 * max(1.0, abs(lb))
+    assert np.array_equal(a.getWeights(), b.getWeights())
+
+
+def test_loss_curve_and_eval(g, orc):
+    dims, B, n, iters = [256, 192, 128, 16], 128, 2048, 40
+    net = wide_net(g, dims)
+    ref = orc.OracleNet(dims)
+    ref.set_weights(net.getWeights())
+    rng = np.random.RandomState(3)
+    centers = rng.rand(16, 256)
+    lab = rng.randint(0, 16, n).astype(np.int32)
+    x = np.clip(centers[lab] + 0.3 * rng.randn(n, 256), 0, 1)
+    t = np.zeros((n, 16))
+    t[np.arange(n), lab] = 1.0
+    ds = g.Dataset(net, x.astype(np.float32), labels=lab)
+    idx = g.Sampler(n, seed=1).draw(iters, B)
+    import ctypes as C
+    losses = np.empty(iters)
+    g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), iters, B,
+                                                 0.05, 0.9, losses.ctypes.data_as(C.POINTER(C.c_double))))
+    ref_losses = ref.train(x, t, iters, B, 0.05, 0.9, idx=idx, want_loss=True)
+    assert np.all(np.abs(losses - ref_losses) <= 5e-2 * np.maximum(1.0, np.abs(ref_losses)))
+    assert losses[-1] < losses[0]
+    hits, mean_loss, pred = ds.evaluate(want_pred=True)
+    rhits, rpred = ref.evaluate(x, lab)
+    assert abs(hits - rhits) <= 0.03 * n                    # two independently trained copies in different precision
+    assert (pred == rpred).mean() >= 0.95
+    assert abs(mean_loss - ref.validate(x, t, n)) <= 5e-2 * max(1.0, mean_loss)
+
+
+def test_eval_argmax_last_max_wins(g):
+    dims = [64, 16]
+    net = wide_net(g, dims)
+    net.setWeights(np.zeros(net.numWeights))
+    x = np.random.RandomState(0).rand(40, 64).astype(np.float32)
+    ds = g.Dataset(net, x, labels=np.full(40, 15, dtype=np.int32))
+    hits, _, pred = ds.evaluate(want_pred=True)
+    assert hits == 40 and (pred == 15).all()                # MNISTTrainer.java:166-168
+
+
+def test_host_pinned_dataset_matches_device(g):
+    dims, B = [256, 128, 32], 64
+    a, b = wide_net(g, dims), wide_net(g, dims)
+    rng = np.random.RandomState(4)
+    x = rng.rand(512, 256).astype(np.float32)
+    lab = rng.randint(0, 32, 512).astype(np.int32)
+    da = g.Dataset(a, x, labels=lab, location=g.capi.DATA_DEVICE)
+    db = g.Dataset(b, x, labels=lab, location=g.capi.DATA_HOST_PINNED)
+    idx = g.Sampler(512, seed=1).draw(6, B)
+    import ctypes as C
+    for net, ds in ((a, da), (b, db)):
+        g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), 6, B,
+                                                     0.05, 0.9, None))
+    assert np.array_equal(a.getWeights(), b.getWeights())
