@@ -49,6 +49,8 @@ SIGNATURES = {
     "b2nn_sync": (C.c_int, [_vp]),
     "b2nn_set_stream": (C.c_int, [_vp, _vp]),
     "b2nn_kernel_launches": (C.c_int, [_vp, _lp]),
+    "b2nn_profile_enable": (C.c_int, [_vp, C.c_int32]),
+    "b2nn_profile_read": (C.c_int, [_vp, _dp, _lp, _dp]),
     "b2nn_device_count": (C.c_int, [_ip]),
     "b2nn_version": (C.c_int, []),
     "b2nn_last_error": (C.c_char_p, []),

@@ -80,6 +80,10 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     net->last_act = last_act; net->last_param = last_param; net->loss = loss;
     net->precision = precision; net->flags = flags;
     net->num_sms = prop.multiProcessorCount;
+    {
+        const char *fu = getenv("B2NN_FUSED_UPDATE");
+        net->fused_update = fu != nullptr && fu[0] == '1';
+    }
     net->w_off.resize(n_dims);
     int64_t tot = 0;
     for (int l = 0; l + 1 < n_dims; l++) { net->w_off[l] = tot; tot += (int64_t)dims[l] * dims[l + 1]; }
@@ -123,6 +127,7 @@ int b2nn_destroy(b2nn_net *net) {
     comm_destroy(net);
     f64_free(net);
     wide_free(net);
+    for (auto e : net->prof_events) cudaEventDestroy(e);
     if (net->pinned) cudaFreeHost(net->pinned);
     if (net->dscratch) cudaFree(net->dscratch);
     if (net->own_stream && net->stream) cudaStreamDestroy(net->stream);
@@ -185,6 +190,29 @@ int b2nn_set_stream(b2nn_net *net, void *cuda_stream) {
 int b2nn_kernel_launches(const b2nn_net *net, int64_t *n) {
     B2_REQUIRE(net != nullptr && n != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
     *n = net->launches;
+    return B2NN_OK;
+}
+
+int b2nn_profile_enable(b2nn_net *net, int32_t on) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    if (on && net->prof_events.empty()) {
+        net->prof_events.resize(4096);
+        for (auto &e : net->prof_events) B2_CHECK_CUDA(cudaEventCreate(&e));
+    }
+    B2_TRY(profile_flush(net));
+    net->profiling = on != 0;
+    net->prof_flops = 0; net->prof_ms_acc = 0; net->prof_launch_acc = 0;
+    return B2NN_OK;
+}
+
+int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, double *gemm_flops) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    B2_TRY(profile_flush(net));
+    if (gemm_ms) *gemm_ms = net->prof_ms_acc;
+    if (gemm_launches) *gemm_launches = net->prof_launch_acc;
+    if (gemm_flops) *gemm_flops = net->prof_flops;
     return B2NN_OK;
 }
 

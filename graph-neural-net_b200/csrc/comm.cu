@@ -96,8 +96,10 @@ int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
     for (int l = 0; l < L; l++) {
         B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->layer_events[l], cudaEventDisableTiming));
         auto &y = net->wide[l];
-        B2_CHECK_CUDA(cudaMalloc(&y.g, (size_t)y.in * y.ld_n * sizeof(float)));
-        B2_CHECK_CUDA(cudaMemset(y.g, 0, (size_t)y.in * y.ld_n * sizeof(float)));
+        if (y.g == nullptr) {
+            B2_CHECK_CUDA(cudaMalloc(&y.g, (size_t)y.in * y.ld_n * sizeof(float)));
+            B2_CHECK_CUDA(cudaMemset(y.g, 0, (size_t)y.in * y.ld_n * sizeof(float)));
+        }
     }
     B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->comm_done, cudaEventDisableTiming));
     return B2NN_OK;

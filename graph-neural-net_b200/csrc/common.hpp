@@ -137,6 +137,7 @@ struct b2nn_net {
     double *f64_grad = nullptr;  // [P] scratch for weight_gradient
 
     // BF16 path
+    bool fused_update = false;  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
     b2nn::WideBatch wb;
 
@@ -145,6 +146,14 @@ struct b2nn_net {
     int rank = 0, world = 1;
     std::vector<cudaEvent_t> layer_events;
     cudaEvent_t comm_done = nullptr;
+
+    // profiling (b2nn_profile_enable): event pairs around GEMM launches
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;  // start/stop pairs
+    size_t prof_used = 0;
+    double prof_flops = 0;
+    double prof_ms_acc = 0;
+    int64_t prof_launch_acc = 0;
 
     // host staging
     void *pinned = nullptr;

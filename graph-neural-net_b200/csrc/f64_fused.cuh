@@ -1,0 +1,324 @@
+// f64_fused.cuh -- K1: persistent fused FP64 training kernel for the reference's small nets
+// (three weight matrices d0-d1-d2-d3, e.g. 784-300-100-10 batch 16).
+//
+// One cooperative launch runs `iters` consecutive mini-batch steps (forward, softmax/CE or general
+// output delta, backprop, batch-summed gradient, momentum update -- SoftmaxCrossEntropyNeuralNet.java
+// :164-198, :229-287, :297-346) with the weights resident in shared memory, distributed over all SMs:
+//   * CTA c owns a slice of the COLUMNS of W0 (and the matching rows of W1 for backprop) and, if
+//     c < d2-slices, a slice of the columns of W1; W2 (tiny) is replicated in every CTA.
+//   * per step only TWO grid-wide barriers: after z1 (layer-1 pre-activations published to L2) and
+//     after z2.  Everything after that -- z3, softmax, delta3, delta2 (replicated, tiny), delta1 for the
+//     CTA's own columns, all gradients and updates -- is CTA-local, so the next step starts without
+//     another barrier.  Replicated weights stay consistent because every replica applies the same
+//     arithmetic to the same inputs in the same order.
+//   * dot products are split over the lanes of a warp and combined with a fixed xor-shuffle tree
+//     (deterministic; order differs from the reference's ascending-i loop => parity by tolerance);
+//     batch sums and the update keep the reference's order and un-fused multiply/add.
+#pragma once
+#include <cstdint>
+
+#include "f64_kernels.cuh"
+
+namespace b2nn {
+namespace f64 {
+
+struct FusedParams {
+    int d0, d1, d2, d3, B, iters;
+    int kind, inner_act, last_act, loss_kind, stable;
+    double inner_p, last_p, step, momentum;
+    const double *X;        // [n][d0] rows (or null when Xu8 is set)
+    const uint8_t *Xu8;     // [n][d0] rows as pixel bytes, value = byte/255.0 (exactly how the rows were made)
+    const double *T;        // [n][d3] dense targets or null
+    const int32_t *labels;  // [n] or null
+    const int32_t *idx;     // [iters][B]
+    double *W0, *W1, *W2, *V0, *V1, *V2;  // canonical [in][out] state (read at start, written at end)
+    double *V0t;            // [d1][d0] scratch: velocity of W0, column-contiguous during the run
+    double *V1b;            // [d1][d2] scratch: velocity replica for the row-slice copy of W1
+    double *V2r;            // [grid][d2*d3] scratch: per-CTA velocity replica of W2
+    double *z1buf;          // [2][B][d1] published pre-activations (double buffered by step parity)
+    double *z2buf;          // [2][B][d2]
+    unsigned long long *bar;  // grid barrier counter (zeroed before launch)
+    double *loss_out;       // [iters] sum over the batch of per-sample losses, or null
+    // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
+    int nc0max, nc1max;
+    int o_a0, o_a1, o_z2, o_a2, o_d2, o_w0, o_w1c, o_w1r, o_w2, o_z1o, o_d1o, o_z3, o_d3, o_t, o_misc;
+};
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1ULL);
+        unsigned long long v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+        } while (v < target);
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ int slice_lo(int c, int n, int G) { return (int)(((long long)c * n) / G); }
+
+// momentum update in the reference's evaluation order (S:333-339)
+__device__ __forceinline__ double sgd_adj(double step, double g, int B, double mom, double prev) {
+    return __dadd_rn(__ddiv_rn(__dmul_rn(step, g), (double)B), __dmul_rn(mom, prev));
+}
+
+__global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p) {
+    extern __shared__ double sm[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = blockDim.x >> 5, NT = blockDim.x;
+    const int c = blockIdx.x, G = gridDim.x;
+    const int d0 = p.d0, d1 = p.d1, d2 = p.d2, d3 = p.d3, B = p.B;
+    const int j0 = slice_lo(c, d1, G), j1 = slice_lo(c + 1, d1, G), nc0 = j1 - j0;  // own columns of W0 / rows of W1
+    const int k0 = slice_lo(c, d2, G), k1 = slice_lo(c + 1, d2, G), nc1 = k1 - k0;  // own columns of W1
+    double *a0 = sm + p.o_a0;    // [B][d0]
+    double *a1 = sm + p.o_a1;    // [B][d1]   (only staged by CTAs that own W1 columns)
+    double *z2 = sm + p.o_z2;    // [B][d2]
+    double *a2 = sm + p.o_a2;    // [B][d2]
+    double *dl2 = sm + p.o_d2;   // [B][d2]
+    double *w0 = sm + p.o_w0;    // [nc0][d0]   column-contiguous
+    double *w1c = sm + p.o_w1c;  // [nc1][d1]   own columns of W1, column-contiguous
+    double *w1r = sm + p.o_w1r;  // [nc0][d2]   own rows of W1
+    double *w2 = sm + p.o_w2;    // [d2][d3]
+    double *z1o = sm + p.o_z1o;  // [B][nc0max] own pre-activations
+    double *d1o = sm + p.o_d1o;  // [B][nc0max] own deltas
+    double *z3 = sm + p.o_z3;    // [B][d3]  (reused for exp terms / activations)
+    double *dl3 = sm + p.o_d3;   // [B][d3]
+    double *tt = sm + p.o_t;     // [B][d3]
+    double *misc = sm + p.o_misc;  // [B] row sums / losses
+
+    // ---- load the CTA's weight slices (and transpose its velocity slices into the scratch layouts) ----
+    for (int e = tid; e < nc0 * d0; e += NT) {
+        const int jj = e / d0, k = e % d0;
+        w0[e] = p.W0[(size_t)k * d1 + j0 + jj];
+        p.V0t[(size_t)(j0 + jj) * d0 + k] = p.V0[(size_t)k * d1 + j0 + jj];
+    }
+    for (int e = tid; e < nc1 * d1; e += NT) {
+        const int kk = e / d1, j = e % d1;
+        w1c[e] = p.W1[(size_t)j * d2 + k0 + kk];
+    }
+    for (int e = tid; e < nc0 * d2; e += NT) {
+        const int jj = e / d2, k = e % d2;
+        w1r[e] = p.W1[(size_t)(j0 + jj) * d2 + k];
+        p.V1b[(size_t)(j0 + jj) * d2 + k] = p.V1[(size_t)(j0 + jj) * d2 + k];
+    }
+    double *v2 = p.V2r + (size_t)c * d2 * d3;
+    for (int e = tid; e < d2 * d3; e += NT) { w2[e] = p.W2[e]; v2[e] = p.V2[e]; }
+    __syncthreads();
+
+    unsigned long long bar_target = 0;
+    for (int it = 0; it < p.iters; it++) {
+        const int32_t *idx = p.idx + (size_t)it * B;
+        double *z1pub = p.z1buf + (size_t)(it & 1) * B * d1;
+        double *z2pub = p.z2buf + (size_t)(it & 1) * B * d2;
+
+        // ---- stage the batch: a0 = f(x) (input layer is activated too, S:183-186), targets ----
+        if (p.Xu8) {
+            for (int e = tid; e < B * d0; e += NT) {
+                const int b = e / d0, k = e % d0;
+                const double x = (double)p.Xu8[(size_t)idx[b] * d0 + k] / 255.0;  // MNISTTrainer.java:97
+                a0[e] = act(p.inner_act, p.inner_p, x);
+            }
+        } else {
+            for (int e = tid; e < B * d0; e += NT) {
+                const int b = e / d0, k = e % d0;
+                a0[e] = act(p.inner_act, p.inner_p, p.X[(size_t)idx[b] * d0 + k]);
+            }
+        }
+        for (int e = tid; e < B * d3; e += NT) {
+            const int b = e / d3, j = e % d3;
+            tt[e] = p.T ? p.T[(size_t)idx[b] * d3 + j] : ((p.labels[idx[b]] == j) ? 1.0 : 0.0);
+        }
+        __syncthreads();
+
+        // ---- phase 1: z1[:, own columns] = a0 . W0[:, own]; publish ----
+        for (int b = warp; b < B; b += NW) {
+            for (int jj = 0; jj < nc0; jj++) {
+                const double *ar = a0 + (size_t)b * d0, *wc = w0 + (size_t)jj * d0;
+                double s0 = 0.0, s1 = 0.0;
+                int k = lane;
+                for (; k + 32 < d0; k += 64) { s0 = fma(ar[k], wc[k], s0); s1 = fma(ar[k + 32], wc[k + 32], s1); }
+                if (k < d0) s0 = fma(ar[k], wc[k], s0);
+                const double z = warp_sum_d(s0 + s1);
+                if (lane == 0) { z1o[b * p.nc0max + jj] = z; z1pub[(size_t)b * d1 + j0 + jj] = z; }
+            }
+        }
+        bar_target += G;
+        grid_barrier(p.bar, bar_target);
+
+        // ---- phase 2: owners of W1 columns: a1 = f(z1) (all of it), z2[:, own] = a1 . W1[:, own]; publish ----
+        if (nc1 > 0) {
+            for (int e = tid; e < B * d1; e += NT) a1[e] = act(p.inner_act, p.inner_p, __ldcg(z1pub + e));
+            __syncthreads();
+            for (int b = warp; b < B; b += NW) {
+                for (int kk = 0; kk < nc1; kk++) {
+                    const double *ar = a1 + (size_t)b * d1, *wc = w1c + (size_t)kk * d1;
+                    double s0 = 0.0, s1 = 0.0;
+                    int j = lane;
+                    for (; j + 32 < d1; j += 64) { s0 = fma(ar[j], wc[j], s0); s1 = fma(ar[j + 32], wc[j + 32], s1); }
+                    if (j < d1) s0 = fma(ar[j], wc[j], s0);
+                    const double z = warp_sum_d(s0 + s1);
+                    if (lane == 0) z2pub[(size_t)b * d2 + k0 + kk] = z;
+                }
+            }
+        }
+        bar_target += G;
+        grid_barrier(p.bar, bar_target);
+
+        // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
+        for (int e = tid; e < B * d2; e += NT) {
+            const double z = __ldcg(z2pub + e);
+            z2[e] = z;
+            a2[e] = act(p.inner_act, p.inner_p, z);
+        }
+        __syncthreads();
+        for (int e = tid; e < B * d3; e += NT) {
+            const int b = e / d3, j = e % d3;
+            const double *ar = a2 + (size_t)b * d2;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int k = 0;
+            for (; k + 3 < d2; k += 4) {
+                s0 = fma(ar[k], w2[k * d3 + j], s0);
+                s1 = fma(ar[k + 1], w2[(k + 1) * d3 + j], s1);
+                s2 = fma(ar[k + 2], w2[(k + 2) * d3 + j], s2);
+                s3 = fma(ar[k + 3], w2[(k + 3) * d3 + j], s3);
+            }
+            for (; k < d2; k++) s0 = fma(ar[k], w2[k * d3 + j], s0);
+            z3[e] = (s0 + s1) + (s2 + s3);
+        }
+        __syncthreads();
+        if (p.kind == 0) {
+            // softmax (S:357-376) + cross entropy (S:213-217) + delta (S:249-251)
+            if (tid < B) {
+                double mx = 0.0;
+                if (p.stable) {
+                    mx = z3[tid * d3];
+                    for (int j = 1; j < d3; j++) mx = fmax(mx, z3[tid * d3 + j]);
+                }
+                misc[tid] = mx;
+            }
+            __syncthreads();
+            for (int e = tid; e < B * d3; e += NT) z3[e] = exp(z3[e] - misc[e / d3]);
+            __syncthreads();
+            if (tid < B) {
+                double sum = 0.0;
+                for (int j = 0; j < d3; j++) sum = __dadd_rn(sum, z3[tid * d3 + j]);  // ascending i like the reference
+                misc[tid] = sum;
+            }
+            __syncthreads();
+            for (int e = tid; e < B * d3; e += NT) {
+                const double pr = __ddiv_rn(z3[e], misc[e / d3]);
+                dl3[e] = __dsub_rn(pr, tt[e]);
+                if (p.loss_out) z3[e] = __dmul_rn(tt[e], log(pr));
+            }
+        } else {
+            // general output layer (G:268-271, G:236-239)
+            for (int e = tid; e < B * d3; e += NT) {
+                const double z = z3[e], a = act(p.last_act, p.last_p, z);
+                dl3[e] = __dmul_rn(loss_prime(p.loss_kind, a, tt[e]), act_prime(p.last_act, p.last_p, z));
+                if (p.loss_out) z3[e] = -loss_fn(p.loss_kind, a, tt[e]);
+            }
+        }
+        __syncthreads();
+        if (p.loss_out && c == 0 && tid == 0) {
+            double tot = 0.0;
+            for (int b = 0; b < B; b++) {
+                double l = 0.0;
+                for (int j = 0; j < d3; j++) l = __dsub_rn(l, z3[b * d3 + j]);
+                tot = __dadd_rn(tot, l);
+            }
+            p.loss_out[it] = tot;
+        }
+        // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
+        for (int e = tid; e < B * d2; e += NT) {
+            const int b = e / d2, j = e % d2;
+            double s = 0.0;
+            for (int k = 0; k < d3; k++) s = __dadd_rn(s, __dmul_rn(w2[j * d3 + k], dl3[b * d3 + k]));
+            dl2[e] = __dmul_rn(s, act_prime(p.inner_act, p.inner_p, z2[e]));
+        }
+        __syncthreads();
+
+        // ---- phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own) ----
+        for (int e = tid; e < B * nc0; e += NT) {
+            const int b = e / nc0, jj = e % nc0;
+            const double *wr = w1r + (size_t)jj * d2, *dr = dl2 + (size_t)b * d2;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int k = 0;
+            for (; k + 3 < d2; k += 4) {
+                s0 = fma(wr[k], dr[k], s0); s1 = fma(wr[k + 1], dr[k + 1], s1);
+                s2 = fma(wr[k + 2], dr[k + 2], s2); s3 = fma(wr[k + 3], dr[k + 3], s3);
+            }
+            for (; k < d2; k++) s0 = fma(wr[k], dr[k], s0);
+            d1o[b * p.nc0max + jj] =
+                __dmul_rn((s0 + s1) + (s2 + s3), act_prime(p.inner_act, p.inner_p, z1o[b * p.nc0max + jj]));
+        }
+        __syncthreads();
+
+        // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
+        // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
+        for (int e = tid; e < nc0 * d0; e += NT) {
+            const int jj = e / d0, k = e % d0;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(d1o[b * p.nc0max + jj], a0[(size_t)b * d0 + k]));
+            double *vp = p.V0t + (size_t)(j0 + jj) * d0 + k;
+            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
+            w0[e] = __dsub_rn(w0[e], adj);
+            *vp = adj;
+        }
+        // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
+        for (int e = tid; e < nc1 * d1; e += NT) {
+            const int kk = e / d1, j = e % d1;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k0 + kk], a1[(size_t)b * d1 + j]));
+            double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
+            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
+            w1c[e] = __dsub_rn(w1c[e], adj);
+            *vp = adj;
+        }
+        // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
+        for (int e = tid; e < nc0 * d2; e += NT) {
+            const int jj = e / d2, k = e % d2;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) {
+                const double a = act(p.inner_act, p.inner_p, z1o[b * p.nc0max + jj]);
+                g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a));
+            }
+            double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
+            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
+            w1r[e] = __dsub_rn(w1r[e], adj);
+            *vp = adj;
+        }
+        // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
+        for (int e = tid; e < d2 * d3; e += NT) {
+            const int i = e / d3, j = e % d3;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl3[b * d3 + j], a2[b * d2 + i]));
+            const double adj = sgd_adj(p.step, g, B, p.momentum, v2[e]);
+            w2[e] = __dsub_rn(w2[e], adj);
+            v2[e] = adj;
+        }
+        __syncthreads();
+    }
+
+    // ---- write the CTA's slices back to the canonical [in][out] state ----
+    for (int e = tid; e < nc0 * d0; e += NT) {
+        const int jj = e / d0, k = e % d0;
+        p.W0[(size_t)k * d1 + j0 + jj] = w0[e];
+        p.V0[(size_t)k * d1 + j0 + jj] = p.V0t[(size_t)(j0 + jj) * d0 + k];
+    }
+    for (int e = tid; e < nc1 * d1; e += NT) {
+        const int kk = e / d1, j = e % d1;
+        p.W1[(size_t)j * d2 + k0 + kk] = w1c[e];  // V1 columns were updated in place
+    }
+    if (c == 0)
+        for (int e = tid; e < d2 * d3; e += NT) { p.W2[e] = w2[e]; p.V2[e] = v2[e]; }
+}
+
+}  // namespace f64
+}  // namespace b2nn

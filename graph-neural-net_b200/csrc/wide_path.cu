@@ -48,6 +48,21 @@ int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t k, uint64_t rows, 
     return B2NN_OK;
 }
 
+// fold the recorded event pairs into the accumulators (synchronises the stream)
+int profile_flush(b2nn_net *net) {
+    if (net->prof_used) {
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        for (size_t i = 0; i + 1 < net->prof_used; i += 2) {
+            float ms = 0.f;
+            B2_CHECK_CUDA(cudaEventElapsedTime(&ms, net->prof_events[i], net->prof_events[i + 1]));
+            net->prof_ms_acc += ms;
+            net->prof_launch_acc++;
+        }
+        net->prof_used = 0;
+    }
+    return B2NN_OK;
+}
+
 template <int EPI>
 static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
     static bool attr_done = false;
@@ -58,7 +73,18 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     }
     const int tiles = ((g.M + GEMM_BM - 1) / GEMM_BM) * ((g.N + GEMM_BN - 1) / GEMM_BN);
     const int grid = tiles < net->num_sms ? tiles : net->num_sms;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (net->profiling) {
+        if (net->prof_used + 2 > net->prof_events.size()) B2_TRY(profile_flush(net));
+        e0 = net->prof_events[net->prof_used++];
+        e1 = net->prof_events[net->prof_used++];
+        B2_CHECK_CUDA(cudaEventRecord(e0, net->stream));
+    }
     gemm_tn_bf16_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
+    if (net->profiling) {
+        B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
+        net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
+    }
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -131,6 +157,10 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         B2_CHECK_CUDA(cudaMalloc(&y.wt, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
         B2_CHECK_CUDA(cudaMemset(y.wn, 0, nf * sizeof(__nv_bfloat16)));
         B2_CHECK_CUDA(cudaMemset(y.wt, 0, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
+        if (!net->fused_update) {
+            B2_CHECK_CUDA(cudaMalloc(&y.g, nf * sizeof(float)));
+            B2_CHECK_CUDA(cudaMemset(y.g, 0, nf * sizeof(float)));
+        }
         B2_TRY(make_tmap_bf16(&y.tm_wt, y.wt, y.in, y.out, y.ld_t, GEMM_BN));  // forward: N=out, K=in
         B2_TRY(make_tmap_bf16(&y.tm_wn, y.wn, y.out, y.in, y.ld_n, GEMM_BN));  // delta:   N=in,  K=out
     }
@@ -275,12 +305,21 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
         GemmArgs g{};
         g.M = y.in; g.N = y.out; g.K = B;
         g.ldw = y.ld_n;
-        if (net->world == 1) {
+        if (net->world == 1 && net->fused_update) {
             g.w = y.w; g.v = y.v;
             g.out0 = y.wn; g.ld0 = y.ld_n;
             g.out1 = y.wt; g.ld1 = y.ld_t;
             g.scale = scale; g.momentum = (float)momentum;
             B2_TRY(launch_gemm<EPI_DW_UPDATE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+        } else if (net->world == 1) {
+            // gradient GEMM stores G (FP32), then the coalesced HBM-bound update kernel (K7)
+            g.w = y.g;
+            B2_TRY(launch_gemm<EPI_DW_STORE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+            dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
+            wide::sgd_update<<<grid, block, 0, net->stream>>>(y.g, y.w, y.v, y.in, y.out, y.ld_n, scale,
+                                                              (float)momentum, 0, y.wn, y.wt, y.ld_t);
+            net->launches++;
+            B2_CHECK_CUDA(cudaGetLastError());
         } else {
             g.w = y.g;
             B2_TRY(launch_gemm<EPI_DW_STORE>(net, b.tm_at[l], b.tm_dt[l + 1], g));

@@ -173,6 +173,15 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_kernel_launches(self._h, C.byref(n)))
         return n.value
 
+    def profileEnable(self, on=True):
+        capi.check(capi.lib().b2nn_profile_enable(self._h, int(on)))
+
+    def profileRead(self):
+        """(gemm_ms, gemm_launches, gemm_flops) since profiling was enabled"""
+        ms, n, fl = C.c_double(), C.c_int64(), C.c_double()
+        capi.check(capi.lib().b2nn_profile_read(self._h, C.byref(ms), C.byref(n), C.byref(fl)))
+        return ms.value, n.value, fl.value
+
     def commInit(self, unique_id, rank, world):
         buf = C.create_string_buffer(bytes(unique_id), 128)
         capi.check(capi.lib().b2nn_comm_init(self._h, buf, rank, world))

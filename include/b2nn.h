@@ -182,6 +182,11 @@ int b2nn_sync(b2nn_net *net);
 int b2nn_set_stream(b2nn_net *net, void *cuda_stream);
 /* number of this library's kernels launched on the handle since creation */
 int b2nn_kernel_launches(const b2nn_net *net, int64_t *n);
+/* Measurement aid: with profiling on, every contraction (GEMM) launch is bracketed by CUDA events
+ * on the launching stream; b2nn_profile_read synchronises and returns the summed device time (ms),
+ * launch count and algorithmic FLOPs (2*M*N*K per launch) since profiling was switched on. */
+int b2nn_profile_enable(b2nn_net *net, int32_t on);
+int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, double *gemm_flops);
 int b2nn_device_count(int32_t *n);
 int b2nn_version(void);
 const char *b2nn_last_error(void);

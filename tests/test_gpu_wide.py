@@ -2,7 +2,9 @@
 
 Tolerances (stated here): BF16 operands (8-bit mantissa) with FP32 accumulation --
   - plain contraction y = x W (identity activations): |diff| <= 2e-2 * max|y|;
-  - one-step update direction: relative Frobenius error <= 3e-2; batch loss within 2e-2 relative;
+  - one-step update: <= 1e-2 relative (Frobenius, per layer) against a numpy model that rounds to
+    BF16 where the kernels do; <= 1e-1 and cosine >= 0.995 against the FP64 oracle (leaky-ReLU slope
+    flips near zero dominate, see test_one_step_vs_bf16_model_and_oracle); batch loss within 2e-2;
   - loss curve over the first 40 steps within 5 % of the oracle's.
 """
 import numpy as np
@@ -71,9 +73,42 @@ def test_weights_roundtrip_and_init(g, orc):
     assert np.array_equal(net.getWeights(), v.astype(np.float32).astype(np.float64))
 
 
+def emulate_bf16_step(dims, w0, x, lab, step, alpha=0.01):
+    """numpy model of the BF16 path: operands rounded to bfloat16 exactly where the kernels round
+    them (a_l, delta_l, the two BF16 weight copies), products accumulated in FP64 (the kernels
+    accumulate in FP32), FP32 master update.  Returns (mean loss, update v = step*G/B per layer)."""
+    L = len(dims) - 1
+    B = x.shape[0]
+    W, off = [], 0
+    for l in range(L):
+        n = dims[l] * dims[l + 1]
+        W.append(w0[off:off + n].reshape(dims[l], dims[l + 1]))
+        off += n
+    leaky = lambda z: np.where(z > 0, z, alpha * z)
+    a = [bf16_round(leaky(x.astype(np.float32).astype(np.float64)))]
+    for l in range(L - 1):
+        a.append(bf16_round(leaky(a[l] @ bf16_round(W[l]))))
+    z = (a[L - 1] @ bf16_round(W[L - 1])).astype(np.float32).astype(np.float64)
+    zs = z - z.max(axis=1, keepdims=True)
+    lse = np.log(np.exp(zs).sum(axis=1, keepdims=True))
+    p = np.exp(zs - lse)
+    loss = float(np.mean(-(zs - lse)[np.arange(B), lab]))
+    t = np.zeros_like(p)
+    t[np.arange(B), lab] = 1.0
+    d = [None] * (L + 1)
+    d[L] = bf16_round(p - t)
+    for l in range(L - 1, 0, -1):
+        d[l] = bf16_round((d[l + 1] @ bf16_round(W[l]).T) * np.where(a[l] > 0, 1.0, alpha))
+    return loss, [step * (a[l].T @ d[l + 1]) / B for l in range(L)]
+
+
 @pytest.mark.parametrize("dims,B", [([512, 384, 256, 100], 256), ([784, 300, 100, 10], 64),
                                      ([1000, 520, 1000], 136)])
-def test_one_step_vs_oracle(g, orc, dims, B):
+def test_one_step_vs_bf16_model_and_oracle(g, orc, dims, B):
+    """Tight check against a numpy model that rounds to BF16 at the same points (<= 1e-2 per layer),
+    loose check against the FP64 oracle: with leaky-ReLU a unit whose pre-activation is within the
+    BF16 noise of zero takes the other slope, so a fraction f of delta entries is off by ~100 % and
+    the Frobenius error is ~sqrt(f) (a few %); hence <= 1e-1 per layer plus cosine >= 0.995."""
     net = wide_net(g, dims)
     ref = orc.OracleNet(dims)
     ref.set_weights(net.getWeights())
@@ -84,18 +119,22 @@ def test_one_step_vs_oracle(g, orc, dims, B):
     t[np.arange(B), lab] = 1.0
     w0 = ref.get_weights()
     ref_loss = np.mean([ref.loss(x[i], t[i]) for i in range(B)])
+    emu_loss, emu_v = emulate_bf16_step(dims, w0, x, lab, 0.05)
     loss = net.gradientStepLabeled(x.astype(np.float32), lab, 0.05, 0.9, returnLoss=True)
     ref.gradient_step(x, t, 0.05, 0.9)
     assert abs(loss - ref_loss) <= 2e-2 * max(1.0, abs(ref_loss))
-    du, du_ref = net.getWeights() - w0, ref.get_weights() - w0
-    # per layer, so a wrong small layer cannot hide behind a big one
+    assert abs(loss - emu_loss) <= 1e-3 * max(1.0, abs(emu_loss))
+    du, du_ref = w0 - net.getWeights(), w0 - ref.get_weights()
+    v = net.getVelocity()
     off = 0
     for l in range(len(dims) - 1):
         n = dims[l] * dims[l + 1]
-        rel = np.linalg.norm(du[off:off + n] - du_ref[off:off + n]) / np.linalg.norm(du_ref[off:off + n])
-        assert rel <= 3e-2, (l, rel)
+        a, r, e = du[off:off + n], du_ref[off:off + n], emu_v[l].ravel()
+        assert np.linalg.norm(a - e) <= 1e-2 * np.linalg.norm(e), (l, np.linalg.norm(a - e) / np.linalg.norm(e))
+        assert np.linalg.norm(a - r) <= 1e-1 * np.linalg.norm(r), (l, np.linalg.norm(a - r) / np.linalg.norm(r))
+        assert a @ r >= 0.995 * np.linalg.norm(a) * np.linalg.norm(r)
+        assert np.linalg.norm(v[off:off + n] - e) <= 1e-2 * np.linalg.norm(e)
         off += n
-    assert np.linalg.norm(net.getVelocity() - ref.get_velocity()) <= 3e-2 * np.linalg.norm(ref.get_velocity())
 
 
 def test_dense_target_step_matches_labeled(g):
