@@ -83,6 +83,10 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     {
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = fu != nullptr && fu[0] == '1';
+        const char *ff = getenv("B2NN_F64_FUSED");
+        net->fused_f64_disabled = ff != nullptr && ff[0] == '0';
+        net->coop_launch = prop.cooperativeLaunch != 0;
+        net->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
     }
     net->w_off.resize(n_dims);
     int64_t tot = 0;
@@ -125,6 +129,7 @@ int b2nn_destroy(b2nn_net *net) {
     cudaSetDevice(net->device);
     cudaDeviceSynchronize();
     comm_destroy(net);
+    f64_fused_free(net);
     f64_free(net);
     wide_free(net);
     for (auto e : net->prof_events) cudaEventDestroy(e);

@@ -104,6 +104,7 @@ struct b2nn_dataset {
     int x_dtype = 0;          // dtype rows are stored in (F64 for F64 nets; as given otherwise)
     void *x = nullptr;        // device rows [n][d0], or pinned host rows (mapped) for HOST_PINNED
     void *x_dev_alias = nullptr;  // device-visible pointer to x
+    uint8_t *xu8 = nullptr;   // FP64 nets: device rows as bytes when every x is exactly byte/255.0 (M:97)
     double *t = nullptr;      // device dense targets [n][dL] (F64) or null
     int32_t *labels = nullptr;  // device labels [n] or null (one-hot targets implied)
     int32_t *labels_eval = nullptr;  // labels used for hit counting: == labels, or derived from t (M:183-186)
@@ -135,6 +136,15 @@ struct b2nn_net {
         double *xin = nullptr;          // staged input rows
     } fw;
     double *f64_grad = nullptr;  // [P] scratch for weight_gradient
+    // K1 persistent fused kernel (f64_fused.cu)
+    struct Fused {
+        double *V0t = nullptr, *V1b = nullptr, *V2r = nullptr, *z1buf = nullptr, *z2buf = nullptr;
+        unsigned long long *bar = nullptr;
+        int cap_B = 0;
+    } fused;
+    bool fused_f64_disabled = false;  // B2NN_F64_FUSED=0 forces the general multi-kernel path
+    bool coop_launch = false;
+    int max_smem_optin = 0;
 
     // BF16 path
     bool fused_update = false;  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(256) gemm_strict(const GemmArgs g) {
 
 // a0 = f(x) for gathered rows (the reference applies the inner activation to the input layer
 // too, S:183-186 with l-1 == 0), and the matching target rows.
-__global__ void gather_rows(const double *X, const double *T, const int32_t *labels, const int32_t *idx, int rows,
+static __global__ void gather_rows(const double *X, const double *T, const int32_t *labels, const int32_t *idx, int rows,
                             int d0, int dL, int act_kind, double act_param, double *a0, double *tout) {
     const int r = blockIdx.x;
     if (r >= rows) return;
@@ -141,7 +141,7 @@ __global__ void gather_rows(const double *X, const double *T, const int32_t *lab
 // Output layer, one thread per row (d_L is small on this path; order kept sequential):
 //  softmax (S:357-376, no max subtraction unless `stable`), loss (S:213-217 / G:236-239),
 //  delta (S:249-251 / G:268-271), `>=` argmax (MNISTTrainer.java:166-168).
-__global__ void output_rows(const double *Z, const double *T, int rows, int dL, int kind, int last_act,
+static __global__ void output_rows(const double *Z, const double *T, int rows, int dL, int kind, int last_act,
                             double last_param, int loss_kind, int stable, double *P, double *loss, double *delta,
                             int32_t *pred) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -186,7 +186,7 @@ __global__ void output_rows(const double *Z, const double *T, int rows, int dL, 
 }
 
 // sequential (row-order) sum of per-row losses and hit count; one thread -- tiny inputs
-__global__ void reduce_rows(const double *loss, const int32_t *pred, const int32_t *labels, int rows,
+static __global__ void reduce_rows(const double *loss, const int32_t *pred, const int32_t *labels, int rows,
                             double *loss_sum, long long *hits) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double s = 0.0;

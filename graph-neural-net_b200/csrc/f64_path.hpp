@@ -15,3 +15,11 @@ int f64_deltas(b2nn_net *net, int rows);
 int f64_gradients(b2nn_net *net, int rows, double step, double momentum, double *grad_out);
 int f64_reduce(b2nn_net *net, int rows, const int32_t *labels_dev, double *loss_sum_dev, long long *hits_dev);
 }  // namespace b2nn
+
+namespace b2nn {
+// K1: persistent fused kernel for three-matrix nets (f64_fused.cu)
+bool f64_fused_supported(b2nn_net *net, int B);
+int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const double *T, const int32_t *labels,
+                    const int32_t *idx_dev, int iters, int B, double step, double momentum, double *loss_dev);
+void f64_fused_free(b2nn_net *net);
+}  // namespace b2nn

@@ -191,3 +191,50 @@ def test_two_layer_and_deep_ragged(g, orc):
             ref.gradient_step(x, t, 0.05, 0.9)
         assert close(net.getWeights(), ref.get_weights(), 1e-12)
         assert close(net.propagate(x), ref.propagate(x), 1e-12)
+
+
+@pytest.mark.parametrize("kind", ["softmax", "general"])
+def test_fused_persistent_kernel_vs_general_path_and_oracle(g, orc, kind, monkeypatch):
+    """K1 (one persistent cooperative kernel for the whole run) against the general multi-kernel
+    path (B2NN_F64_FUSED=0) and the oracle, on non-pixel inputs and ragged dims / batch."""
+    dims, B, iters, n = [33, 47, 21, 7], 5, 60, 400
+    cfg = dict(kind=kind)
+    rng = np.random.RandomState(11)
+    x = rng.randn(n, 33) * 0.7                      # not k/255: exercises the FP64-row loader
+    lab = rng.randint(0, 7, n).astype(np.int32)
+    t = np.zeros((n, 7))
+    t[np.arange(n), lab] = 1.0
+    idx = g.Sampler(n, seed=1).draw(iters, B)
+    results = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("B2NN_F64_FUSED", mode)
+        net, ref = make_nets(g, orc, cfg, dims)
+        tr = g.NeuralNetTrainer((x, t), net)
+        losses = tr.trainIndexed(idx, 0.02, 0.9, wantLoss=True)
+        results[mode] = (net.getWeights(), net.getVelocity(), losses, net.kernelLaunches())
+    ref_losses = ref.train(x, t, iters, B, 0.02, 0.9, idx=idx, want_loss=True)
+    wr, vr = ref.get_weights(), ref.get_velocity()
+    for mode in ("1", "0"):
+        w, v, losses, _ = results[mode]
+        assert np.all(np.abs(losses - ref_losses) <= 1e-10 * np.maximum(1.0, np.abs(ref_losses))), mode
+        assert close(w, wr, 1e-10) and close(v, vr, 1e-10), mode
+    assert results["1"][3] < results["0"][3] / 20    # the fused run is a handful of launches
+
+
+def test_fused_kernel_pixel_bytes_equal_double_rows(g, orc, monkeypatch):
+    """rows that are exactly byte/255.0 are staged as bytes for K1; the result must be identical to
+    feeding the same doubles through the FP64-row loader (a perturbed copy defeats the detection)."""
+    dims, B, iters, n = [784, 100, 50, 10], 8, 40, 600
+    x, t, lab = make_data(n, 784, 10, 13)
+    idx = g.Sampler(n, seed=1).draw(iters, B)
+    out = []
+    for perturb in (False, True):
+        net, _ = make_nets(g, orc, CONFIGS["C1"], dims)
+        xx = x.copy()
+        if perturb:
+            xx[-1, -1] = 0.123456789                # row n-1 is never drawn below
+        idx2 = np.where(idx == n - 1, 0, idx).astype(np.int32)
+        tr = g.NeuralNetTrainer((xx, t), net)
+        tr.trainIndexed(idx2, 0.01, 0.9)
+        out.append(net.getWeights())
+    assert np.array_equal(out[0], out[1])
