@@ -95,10 +95,15 @@ class ClockSampler(threading.Thread):
 
 
 def synth_data(rows, d0, n_classes, seed, dtype):
-    """x ~ U[0,1) (pixel-like), labels uniform; seeded"""
+    """x ~ U[0,1) (pixel-like), labels uniform; seeded.  FP64 rows are made the way the
+    reference makes MNIST rows -- (byte & 0xff) / 255.0, MNISTTrainer.java:97 -- with MNIST's ~80 % zeros."""
     rng = np.random.default_rng(seed)
-    x = rng.random((rows, d0), dtype=np.float32)
     labels = rng.integers(0, n_classes, rows).astype(np.int32)
+    if dtype == np.float64:
+        raw = rng.integers(0, 256, (rows, d0), dtype=np.uint8)
+        raw[rng.random((rows, d0), dtype=np.float32) < 0.8] = 0
+        return raw.astype(np.float64) / 255.0, labels
+    x = rng.random((rows, d0), dtype=np.float32)
     return x.astype(dtype, copy=False), labels
 
 
@@ -318,7 +323,6 @@ def tiny_config_line(g, torch, device):
     stream = torch.cuda.current_stream()
     net.setStream(stream.cuda_stream)
     x, labels = synth_data(60000, 784, 10, 1, np.float64)
-    x[x < 0.6] = 0.0
     ds = g.Dataset(net, x, labels=labels)
     smp = g.Sampler(60000, seed=1)
     import ctypes as C

@@ -26,7 +26,6 @@ void make_layout(const b2nn_net *net, int B, int G, Layout *out) {
     auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };
     p.o_a0 = take(B * d0);
     p.o_a1 = take(B * d1);
-    p.o_z2 = take(B * d2);
     p.o_a2 = take(B * d2);
     p.o_d2 = take(B * d2);
     p.o_w0 = take(p.nc0max * d0);
@@ -39,7 +38,20 @@ void make_layout(const b2nn_net *net, int B, int G, Layout *out) {
     p.o_d3 = take(B * d3);
     p.o_t = take(B * d3);
     p.o_misc = take(B);
+    p.o_w2t = take(d2 * d3);
+    p.o_lut = take(256);
+    p.o_stage = take((B * d0 + 7) / 8);  // one batch of rows as bytes
+    p.o_mbar = take(2);
     out->smem_bytes = (size_t)o * sizeof(double);
+}
+const void *fused_kernel_for(int act) {
+    switch (act) {
+    case 0: return (const void *)f64::fused_train_kernel<0>;
+    case 1: return (const void *)f64::fused_train_kernel<1>;
+    case 2: return (const void *)f64::fused_train_kernel<2>;
+    case 3: return (const void *)f64::fused_train_kernel<3>;
+    default: return (const void *)f64::fused_train_kernel<4>;
+    }
 }
 }  // namespace
 
@@ -73,8 +85,8 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
         B2_CHECK_CUDA(cudaMalloc(&fs.V1b, (size_t)d1 * d2 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.V2r, (size_t)G * d2 * d3 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.bar, sizeof(unsigned long long)));
-        B2_CHECK_CUDA(cudaFuncSetAttribute(f64::fused_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           net->max_smem_optin));
+        B2_CHECK_CUDA(cudaFuncSetAttribute(fused_kernel_for(net->inner_act),
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, net->max_smem_optin));
     }
     p.iters = iters;
     p.kind = net->kind; p.inner_act = net->inner_act; p.last_act = net->last_act; p.loss_kind = net->loss;
@@ -85,9 +97,12 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     p.V0 = net->f64[0].v; p.V1 = net->f64[1].v; p.V2 = net->f64[2].v;
     p.V0t = fs.V0t; p.V1b = fs.V1b; p.V2r = fs.V2r; p.z1buf = fs.z1buf; p.z2buf = fs.z2buf; p.bar = fs.bar;
     p.loss_out = loss_dev;
+    // cp.async.bulk needs 16-byte aligned rows (global source, shared destination) and sizes
+    p.bulk = Xu8 ? (d0 % 16 == 0) : (d0 % 2 == 0);
+    if (getenv("B2NN_F64_NO_BULK")) p.bulk = 0;
     B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, sizeof(unsigned long long), net->stream));
     void *args[] = {(void *)&p};
-    B2_CHECK_CUDA(cudaLaunchCooperativeKernel((const void *)f64::fused_train_kernel, dim3(G), dim3(256), args,
+    B2_CHECK_CUDA(cudaLaunchCooperativeKernel(fused_kernel_for(net->inner_act), dim3(G), dim3(512), args,
                                               lo.smem_bytes, net->stream));
     net->launches++;
     return B2NN_OK;

@@ -41,7 +41,10 @@ struct FusedParams {
     double *loss_out;       // [iters] sum over the batch of per-sample losses, or null
     // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
     int nc0max, nc1max;
-    int o_a0, o_a1, o_z2, o_a2, o_d2, o_w0, o_w1c, o_w1r, o_w2, o_z1o, o_d1o, o_z3, o_d3, o_t, o_misc;
+    int o_a0, o_a1, o_a2, o_d2, o_w0, o_w1c, o_w1r, o_w2, o_z1o, o_d1o, o_z3, o_d3, o_t, o_misc;
+    int o_w2t;  // [d3][d2] transposed copy of W2 for the delta2 pass
+    int o_lut, o_stage, o_mbar;  // 256-entry f(byte/255) table, byte staging for one batch, mbarrier
+    int bulk;                    // rows can be fetched with cp.async.bulk (16-byte aligned rows)
 };
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -63,54 +66,106 @@ __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned l
     __syncthreads();
 }
 
+// ---- async bulk copy (TMA, 1-D) of one dataset row into shared memory, completion on an mbarrier ----
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bulk_row_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_expect(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_parity(uint64_t *bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n\t.reg .pred P;\n\tmbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\tselp.b32 %0, 1, 0, P;\n\t}\n"
+            : "=r"(ok)
+            : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+    }
+}
+
 __device__ __forceinline__ int slice_lo(int c, int n, int G) { return (int)(((long long)c * n) / G); }
 
 // momentum update in the reference's evaluation order (S:333-339)
-__device__ __forceinline__ double sgd_adj(double step, double g, int B, double mom, double prev) {
-    return __dadd_rn(__ddiv_rn(__dmul_rn(step, g), (double)B), __dmul_rn(mom, prev));
+// (x / B is computed as x * (1/B) when B is a power of two: bit-identical, no divide)
+__device__ __forceinline__ double sgd_adj(double step, double g, int B, double invB, double mom, double prev) {
+    const double sg = __dmul_rn(step, g);
+    const double q = (invB != 0.0) ? __dmul_rn(sg, invB) : __ddiv_rn(sg, (double)B);
+    return __dadd_rn(q, __dmul_rn(mom, prev));
 }
 
-__global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p) {
+// issue the asynchronous fetch of the batch of step `it` (rows named by idx) into `dst`
+__device__ __forceinline__ void issue_batch_fetch(const FusedParams &p, int it, void *dst, uint64_t *mbar) {
+    const int32_t *idx = p.idx + (size_t)it * p.B;
+    const uint32_t row_bytes = p.Xu8 ? (uint32_t)p.d0 : (uint32_t)p.d0 * 8u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy accesses to dst are done
+    mbar_expect(mbar, row_bytes * (uint32_t)p.B);
+    for (int b = 0; b < p.B; b++) {
+        const size_t row = (size_t)idx[b];
+        const void *src = p.Xu8 ? (const void *)(p.Xu8 + row * p.d0) : (const void *)(p.X + row * p.d0);
+        bulk_row_load((char *)dst + (size_t)b * row_bytes, src, row_bytes, mbar);
+    }
+}
+
+template <int IACT>
+__global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p) {
     extern __shared__ double sm[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = blockDim.x >> 5, NT = blockDim.x;
     const int c = blockIdx.x, G = gridDim.x;
     const int d0 = p.d0, d1 = p.d1, d2 = p.d2, d3 = p.d3, B = p.B;
     const int j0 = slice_lo(c, d1, G), j1 = slice_lo(c + 1, d1, G), nc0 = j1 - j0;  // own columns of W0 / rows of W1
     const int k0 = slice_lo(c, d2, G), k1 = slice_lo(c + 1, d2, G), nc1 = k1 - k0;  // own columns of W1
+    const int ncm = p.nc0max;
+    const double invB = ((B & (B - 1)) == 0) ? 1.0 / (double)B : 0.0;
     double *a0 = sm + p.o_a0;    // [B][d0]
     double *a1 = sm + p.o_a1;    // [B][d1]   (only staged by CTAs that own W1 columns)
-    double *z2 = sm + p.o_z2;    // [B][d2]
     double *a2 = sm + p.o_a2;    // [B][d2]
     double *dl2 = sm + p.o_d2;   // [B][d2]
     double *w0 = sm + p.o_w0;    // [nc0][d0]   column-contiguous
     double *w1c = sm + p.o_w1c;  // [nc1][d1]   own columns of W1, column-contiguous
     double *w1r = sm + p.o_w1r;  // [nc0][d2]   own rows of W1
     double *w2 = sm + p.o_w2;    // [d2][d3]
+    double *w2t = sm + p.o_w2t;  // [d3][d2]
     double *z1o = sm + p.o_z1o;  // [B][nc0max] own pre-activations
     double *d1o = sm + p.o_d1o;  // [B][nc0max] own deltas
-    double *z3 = sm + p.o_z3;    // [B][d3]  (reused for exp terms / activations)
+    double *z3 = sm + p.o_z3;    // [B][d3]  (reused for exp terms / loss terms)
     double *dl3 = sm + p.o_d3;   // [B][d3]
     double *tt = sm + p.o_t;     // [B][d3]
-    double *misc = sm + p.o_misc;  // [B] row sums / losses
+    double *misc = sm + p.o_misc;  // [B] row maxima / sums
+    double *lut = sm + p.o_lut;  // [256] f(byte / 255.0)
+    uint8_t *stage = reinterpret_cast<uint8_t *>(sm + p.o_stage);  // [B][d0] bytes
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(sm + p.o_mbar);
+    const bool u8 = p.Xu8 != nullptr;
 
-    // ---- load the CTA's weight slices (and transpose its velocity slices into the scratch layouts) ----
-    for (int e = tid; e < nc0 * d0; e += NT) {
-        const int jj = e / d0, k = e % d0;
-        w0[e] = p.W0[(size_t)k * d1 + j0 + jj];
-        p.V0t[(size_t)(j0 + jj) * d0 + k] = p.V0[(size_t)k * d1 + j0 + jj];
+    // ---- one-time setup: weight slices into shared memory, velocity slices into the scratch layouts ----
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(mbar)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int e = tid; e < nc1 * d1; e += NT) {
-        const int kk = e / d1, j = e % d1;
-        w1c[e] = p.W1[(size_t)j * d2 + k0 + kk];
-    }
-    for (int e = tid; e < nc0 * d2; e += NT) {
-        const int jj = e / d2, k = e % d2;
-        w1r[e] = p.W1[(size_t)(j0 + jj) * d2 + k];
-        p.V1b[(size_t)(j0 + jj) * d2 + k] = p.V1[(size_t)(j0 + jj) * d2 + k];
-    }
+    for (int jj = 0; jj < nc0; jj++)
+        for (int k = tid; k < d0; k += NT) {
+            w0[jj * d0 + k] = p.W0[(size_t)k * d1 + j0 + jj];
+            p.V0t[(size_t)(j0 + jj) * d0 + k] = p.V0[(size_t)k * d1 + j0 + jj];
+        }
+    for (int kk = 0; kk < nc1; kk++)
+        for (int j = tid; j < d1; j += NT) w1c[kk * d1 + j] = p.W1[(size_t)j * d2 + k0 + kk];
+    for (int jj = 0; jj < nc0; jj++)
+        for (int k = tid; k < d2; k += NT) {
+            w1r[jj * d2 + k] = p.W1[(size_t)(j0 + jj) * d2 + k];
+            p.V1b[(size_t)(j0 + jj) * d2 + k] = p.V1[(size_t)(j0 + jj) * d2 + k];
+        }
     double *v2 = p.V2r + (size_t)c * d2 * d3;
-    for (int e = tid; e < d2 * d3; e += NT) { w2[e] = p.W2[e]; v2[e] = p.V2[e]; }
+    for (int e = tid; e < d2 * d3; e += NT) {
+        w2[e] = p.W2[e]; v2[e] = p.V2[e];
+        w2t[(e % d3) * d2 + e / d3] = p.W2[e];
+    }
+    if (u8 && tid < 256) lut[tid] = act(IACT, p.inner_p, (double)tid / 255.0);  // MNISTTrainer.java:97 + S:185
     __syncthreads();
+    if (p.bulk && tid == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar);
 
     unsigned long long bar_target = 0;
     for (int it = 0; it < p.iters; it++) {
@@ -118,35 +173,42 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p
         double *z1pub = p.z1buf + (size_t)(it & 1) * B * d1;
         double *z2pub = p.z2buf + (size_t)(it & 1) * B * d2;
 
-        // ---- stage the batch: a0 = f(x) (input layer is activated too, S:183-186), targets ----
-        if (p.Xu8) {
-            for (int e = tid; e < B * d0; e += NT) {
-                const int b = e / d0, k = e % d0;
-                const double x = (double)p.Xu8[(size_t)idx[b] * d0 + k] / 255.0;  // MNISTTrainer.java:97
-                a0[e] = act(p.inner_act, p.inner_p, x);
-            }
-        } else {
-            for (int e = tid; e < B * d0; e += NT) {
-                const int b = e / d0, k = e % d0;
-                a0[e] = act(p.inner_act, p.inner_p, p.X[(size_t)idx[b] * d0 + k]);
-            }
-        }
+        // ---- stage the batch: a0 = f(x) (the input layer is activated too, S:183-186) and the targets ----
         for (int e = tid; e < B * d3; e += NT) {
-            const int b = e / d3, j = e % d3;
+            const int b = e / d3, j = e - b * d3;
             tt[e] = p.T ? p.T[(size_t)idx[b] * d3 + j] : ((p.labels[idx[b]] == j) ? 1.0 : 0.0);
         }
+        if (p.bulk) {
+            mbar_wait_parity(mbar, (uint32_t)(it & 1));
+            if (u8) {
+                for (int b = warp; b < B; b += NW)
+                    for (int k = lane; k < d0; k += 32) a0[b * d0 + k] = lut[stage[b * d0 + k]];
+            } else {
+                for (int b = warp; b < B; b += NW)
+                    for (int k = lane; k < d0; k += 32) a0[b * d0 + k] = act(IACT, p.inner_p, a0[b * d0 + k]);
+            }
+        } else {
+            for (int b = warp; b < B; b += NW) {
+                const size_t row = (size_t)idx[b] * d0;
+                for (int k = lane; k < d0; k += 32)
+                    a0[b * d0 + k] = u8 ? lut[p.Xu8[row + k]] : act(IACT, p.inner_p, p.X[row + k]);
+            }
+        }
         __syncthreads();
+        // the byte staging buffer is free again: fetch the NEXT batch while this step computes
+        if (p.bulk && u8 && tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar);
 
         // ---- phase 1: z1[:, own columns] = a0 . W0[:, own]; publish ----
         for (int b = warp; b < B; b += NW) {
+            const double *ar = a0 + (size_t)b * d0;
             for (int jj = 0; jj < nc0; jj++) {
-                const double *ar = a0 + (size_t)b * d0, *wc = w0 + (size_t)jj * d0;
+                const double *wc = w0 + (size_t)jj * d0;
                 double s0 = 0.0, s1 = 0.0;
                 int k = lane;
                 for (; k + 32 < d0; k += 64) { s0 = fma(ar[k], wc[k], s0); s1 = fma(ar[k + 32], wc[k + 32], s1); }
                 if (k < d0) s0 = fma(ar[k], wc[k], s0);
                 const double z = warp_sum_d(s0 + s1);
-                if (lane == 0) { z1o[b * p.nc0max + jj] = z; z1pub[(size_t)b * d1 + j0 + jj] = z; }
+                if (lane == 0) { z1o[b * ncm + jj] = z; z1pub[(size_t)b * d1 + j0 + jj] = z; }
             }
         }
         bar_target += G;
@@ -154,11 +216,24 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p
 
         // ---- phase 2: owners of W1 columns: a1 = f(z1) (all of it), z2[:, own] = a1 . W1[:, own]; publish ----
         if (nc1 > 0) {
-            for (int e = tid; e < B * d1; e += NT) a1[e] = act(p.inner_act, p.inner_p, __ldcg(z1pub + e));
+            {
+                const int n = B * d1;
+                int e = tid;
+                for (; e + 3 * NT < n; e += 4 * NT) {  // 4 independent L2 loads in flight per thread
+                    const double q0 = __ldcg(z1pub + e), q1 = __ldcg(z1pub + e + NT), q2 = __ldcg(z1pub + e + 2 * NT),
+                                 q3 = __ldcg(z1pub + e + 3 * NT);
+                    a1[e] = act(IACT, p.inner_p, q0);
+                    a1[e + NT] = act(IACT, p.inner_p, q1);
+                    a1[e + 2 * NT] = act(IACT, p.inner_p, q2);
+                    a1[e + 3 * NT] = act(IACT, p.inner_p, q3);
+                }
+                for (; e < n; e += NT) a1[e] = act(IACT, p.inner_p, __ldcg(z1pub + e));
+            }
             __syncthreads();
             for (int b = warp; b < B; b += NW) {
+                const double *ar = a1 + (size_t)b * d1;
                 for (int kk = 0; kk < nc1; kk++) {
-                    const double *ar = a1 + (size_t)b * d1, *wc = w1c + (size_t)kk * d1;
+                    const double *wc = w1c + (size_t)kk * d1;
                     double s0 = 0.0, s1 = 0.0;
                     int j = lane;
                     for (; j + 32 < d1; j += 64) { s0 = fma(ar[j], wc[j], s0); s1 = fma(ar[j + 32], wc[j + 32], s1); }
@@ -172,14 +247,30 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p
         grid_barrier(p.bar, bar_target);
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
-        for (int e = tid; e < B * d2; e += NT) {
-            const double z = __ldcg(z2pub + e);
-            z2[e] = z;
-            a2[e] = act(p.inner_act, p.inner_p, z);
+        {
+            const int n = B * d2;
+            int e = tid;
+            for (; e + 3 * NT < n; e += 4 * NT) {
+                const double q0 = __ldcg(z2pub + e), q1 = __ldcg(z2pub + e + NT), q2 = __ldcg(z2pub + e + 2 * NT),
+                             q3 = __ldcg(z2pub + e + 3 * NT);
+                dl2[e] = act_prime(IACT, p.inner_p, q0);           // f'(z2), multiplied into delta2 below
+                dl2[e + NT] = act_prime(IACT, p.inner_p, q1);
+                dl2[e + 2 * NT] = act_prime(IACT, p.inner_p, q2);
+                dl2[e + 3 * NT] = act_prime(IACT, p.inner_p, q3);
+                a2[e] = act(IACT, p.inner_p, q0);
+                a2[e + NT] = act(IACT, p.inner_p, q1);
+                a2[e + 2 * NT] = act(IACT, p.inner_p, q2);
+                a2[e + 3 * NT] = act(IACT, p.inner_p, q3);
+            }
+            for (; e < n; e += NT) {
+                const double z = __ldcg(z2pub + e);
+                dl2[e] = act_prime(IACT, p.inner_p, z);
+                a2[e] = act(IACT, p.inner_p, z);
+            }
         }
         __syncthreads();
         for (int e = tid; e < B * d3; e += NT) {
-            const int b = e / d3, j = e % d3;
+            const int b = e / d3, j = e - b * d3;
             const double *ar = a2 + (size_t)b * d2;
             double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
             int k = 0;
@@ -236,17 +327,17 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p
             p.loss_out[it] = tot;
         }
         // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
-        for (int e = tid; e < B * d2; e += NT) {
-            const int b = e / d2, j = e % d2;
-            double s = 0.0;
-            for (int k = 0; k < d3; k++) s = __dadd_rn(s, __dmul_rn(w2[j * d3 + k], dl3[b * d3 + k]));
-            dl2[e] = __dmul_rn(s, act_prime(p.inner_act, p.inner_p, z2[e]));
-        }
+        for (int b = warp; b < B; b += NW)
+            for (int j = lane; j < d2; j += 32) {
+                double s = 0.0;
+                for (int k = 0; k < d3; k++) s = __dadd_rn(s, __dmul_rn(w2t[k * d2 + j], dl3[b * d3 + k]));
+                dl2[b * d2 + j] = __dmul_rn(s, dl2[b * d2 + j]);
+            }
         __syncthreads();
 
         // ---- phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own) ----
         for (int e = tid; e < B * nc0; e += NT) {
-            const int b = e / nc0, jj = e % nc0;
+            const int b = e / nc0, jj = e - b * nc0;
             const double *wr = w1r + (size_t)jj * d2, *dr = dl2 + (size_t)b * d2;
             double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
             int k = 0;
@@ -255,67 +346,75 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const FusedParams p
                 s2 = fma(wr[k + 2], dr[k + 2], s2); s3 = fma(wr[k + 3], dr[k + 3], s3);
             }
             for (; k < d2; k++) s0 = fma(wr[k], dr[k], s0);
-            d1o[b * p.nc0max + jj] =
-                __dmul_rn((s0 + s1) + (s2 + s3), act_prime(p.inner_act, p.inner_p, z1o[b * p.nc0max + jj]));
+            d1o[b * ncm + jj] = __dmul_rn((s0 + s1) + (s2 + s3), act_prime(IACT, p.inner_p, z1o[b * ncm + jj]));
         }
         __syncthreads();
 
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
-        for (int e = tid; e < nc0 * d0; e += NT) {
-            const int jj = e / d0, k = e % d0;
-            double g = 0.0;
-            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(d1o[b * p.nc0max + jj], a0[(size_t)b * d0 + k]));
-            double *vp = p.V0t + (size_t)(j0 + jj) * d0 + k;
-            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
-            w0[e] = __dsub_rn(w0[e], adj);
-            *vp = adj;
+        for (int jj = 0; jj < nc0; jj++)
+            for (int k = tid; k < d0; k += NT) {
+                double *vp = p.V0t + (size_t)(j0 + jj) * d0 + k;
+                const double vprev = *vp;
+                double g = 0.0;
+                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(d1o[b * ncm + jj], a0[(size_t)b * d0 + k]));
+                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+                w0[jj * d0 + k] = __dsub_rn(w0[jj * d0 + k], adj);
+                *vp = adj;
+            }
+        if (p.bulk && !u8) {
+            // a0 is no longer needed: fetch the next batch's FP64 rows into it while W1 / W2 are updated
+            __syncthreads();
+            if (tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar);
         }
         // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
-        for (int e = tid; e < nc1 * d1; e += NT) {
-            const int kk = e / d1, j = e % d1;
-            double g = 0.0;
-            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k0 + kk], a1[(size_t)b * d1 + j]));
-            double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
-            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
-            w1c[e] = __dsub_rn(w1c[e], adj);
-            *vp = adj;
-        }
-        // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
-        for (int e = tid; e < nc0 * d2; e += NT) {
-            const int jj = e / d2, k = e % d2;
-            double g = 0.0;
-            for (int b = 0; b < B; b++) {
-                const double a = act(p.inner_act, p.inner_p, z1o[b * p.nc0max + jj]);
-                g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a));
+        for (int kk = 0; kk < nc1; kk++)
+            for (int j = tid; j < d1; j += NT) {
+                double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
+                const double vprev = *vp;
+                double g = 0.0;
+                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k0 + kk], a1[(size_t)b * d1 + j]));
+                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+                w1c[kk * d1 + j] = __dsub_rn(w1c[kk * d1 + j], adj);
+                *vp = adj;
             }
-            double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
-            const double adj = sgd_adj(p.step, g, B, p.momentum, *vp);
-            w1r[e] = __dsub_rn(w1r[e], adj);
-            *vp = adj;
-        }
+        // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
+        for (int jj = 0; jj < nc0; jj++)
+            for (int k = tid; k < d2; k += NT) {
+                double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
+                const double vprev = *vp;
+                double g = 0.0;
+                for (int b = 0; b < B; b++) {
+                    const double a = act(IACT, p.inner_p, z1o[b * ncm + jj]);
+                    g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a));
+                }
+                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+                w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
+                *vp = adj;
+            }
         // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
         for (int e = tid; e < d2 * d3; e += NT) {
-            const int i = e / d3, j = e % d3;
+            const int i = e / d3, j = e - i * d3;
+            const double vprev = v2[e];
             double g = 0.0;
             for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl3[b * d3 + j], a2[b * d2 + i]));
-            const double adj = sgd_adj(p.step, g, B, p.momentum, v2[e]);
-            w2[e] = __dsub_rn(w2[e], adj);
+            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+            const double wn = __dsub_rn(w2[e], adj);
+            w2[e] = wn;
+            w2t[j * d2 + i] = wn;
             v2[e] = adj;
         }
         __syncthreads();
     }
 
     // ---- write the CTA's slices back to the canonical [in][out] state ----
-    for (int e = tid; e < nc0 * d0; e += NT) {
-        const int jj = e / d0, k = e % d0;
-        p.W0[(size_t)k * d1 + j0 + jj] = w0[e];
-        p.V0[(size_t)k * d1 + j0 + jj] = p.V0t[(size_t)(j0 + jj) * d0 + k];
-    }
-    for (int e = tid; e < nc1 * d1; e += NT) {
-        const int kk = e / d1, j = e % d1;
-        p.W1[(size_t)j * d2 + k0 + kk] = w1c[e];  // V1 columns were updated in place
-    }
+    for (int jj = 0; jj < nc0; jj++)
+        for (int k = tid; k < d0; k += NT) {
+            p.W0[(size_t)k * d1 + j0 + jj] = w0[jj * d0 + k];
+            p.V0[(size_t)k * d1 + j0 + jj] = p.V0t[(size_t)(j0 + jj) * d0 + k];
+        }
+    for (int kk = 0; kk < nc1; kk++)
+        for (int j = tid; j < d1; j += NT) p.W1[(size_t)j * d2 + k0 + kk] = w1c[kk * d1 + j];  // V1 updated in place
     if (c == 0)
         for (int e = tid; e < d2 * d3; e += NT) { p.W2[e] = w2[e]; p.V2[e] = v2[e]; }
 }

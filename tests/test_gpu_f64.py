@@ -113,7 +113,9 @@ def test_trainer_indexed_run_and_eval(g, orc, name):
     x, t, lab = make_data(n, 784, 10, 3)
     tr = g.NeuralNetTrainer((x, t), net)
     idx = g.Sampler(n, seed=1).draw(iters, B)
+    l0 = net.kernelLaunches()
     losses = tr.trainIndexed(idx, cfg["step"], 0.9, wantLoss=True)
+    assert net.kernelLaunches() - l0 == 1          # the whole run is ONE persistent kernel (K1), no fallback
     ref_losses = ref.train(x, t, iters, B, cfg["step"], 0.9, idx=idx, want_loss=True)
     assert np.all(np.abs(losses - ref_losses) <= 1e-9 * np.maximum(1.0, np.abs(ref_losses)))
     wg, wr = net.getWeights(), ref.get_weights()
