@@ -36,8 +36,10 @@ void make_layout(const b2nn_net *net, int B, int G, Layout *out) {
     p.o_d1o = take(B * p.nc0max);
     p.o_z3 = take(B * d3);
     p.o_d3 = take(B * d3);
-    p.o_t = take(B * d3);
+    p.o_t = take(2 * B * d3);
     p.o_misc = take(B);
+    p.o_a1o = take(B * p.nc0max);
+    p.o_part = take(16 * 4 * 4 + B * 4);  // KS*B <= max(NW*4, B) rows of 4
     p.o_w2t = take(d2 * d3);
     p.o_lut = take(256);
     p.o_stage = take((B * d0 + 7) / 8);  // one batch of rows as bytes
@@ -58,6 +60,8 @@ const void *fused_kernel_for(int act) {
 bool f64_fused_supported(b2nn_net *net, int B) {
     if (net->fused_f64_disabled || net->precision != B2NN_PREC_F64) return false;
     if (net->n_dims != 4 || B < 1 || B > kMaxBatch) return false;
+    if ((net->dims[1] + net->num_sms - 1) / net->num_sms > 4 || (net->dims[2] + net->num_sms - 1) / net->num_sms > 4)
+        return false;  // at most FUSED_CMAX columns per CTA
     if (!net->coop_launch) return false;
     Layout lo;
     make_layout(net, B, net->num_sms, &lo);

@@ -42,6 +42,7 @@ struct FusedParams {
     // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
     int nc0max, nc1max;
     int o_a0, o_a1, o_a2, o_d2, o_w0, o_w1c, o_w1r, o_w2, o_z1o, o_d1o, o_z3, o_d3, o_t, o_misc;
+    int o_a1o, o_part;  // own activations [B][nc0max]; chunk partial sums [KS][B][4]
     int o_w2t;  // [d3][d2] transposed copy of W2 for the delta2 pass
     int o_lut, o_stage, o_mbar;  // 256-entry f(byte/255) table, byte staging for one batch, mbarrier
     int bulk;                    // rows can be fetched with cp.async.bulk (16-byte aligned rows)
@@ -98,6 +99,51 @@ __device__ __forceinline__ double sgd_adj(double step, double g, int B, double i
     return __dadd_rn(q, __dmul_rn(mom, prev));
 }
 
+// Register-blocked partial dot products out of shared memory (the loops are shared-memory-bandwidth
+// bound, so every loaded operand is reused): warp unit (rg, ks) handles rows 4*rg..4*rg+3, all nc <= 4
+// columns, and the ks-th of KS contiguous chunks of K; lanes stride over k.  part[ks][b][c] receives the
+// chunk sums (fixed xor-shuffle tree); the caller adds the KS chunks in ascending ks (deterministic).
+constexpr int FUSED_CMAX = 4;
+__device__ __forceinline__ int fused_ksplit(int B, int NW) {
+    const int RG = (B + 3) / 4;
+    return RG >= NW ? 1 : NW / RG;
+}
+__device__ __forceinline__ void blocked_dot(const double *A, const double *Wc, int B, int K, int nc, double *part,
+                                            int warp, int lane, int NW) {
+    const int RG = (B + 3) / 4, KS = fused_ksplit(B, NW);
+    const int kchunk = (K + KS - 1) / KS;
+    for (int u = warp; u < RG * KS; u += NW) {
+        const int rg = u / KS, ks = u - rg * KS;
+        const int kb = ks * kchunk, ke = min(K, kb + kchunk);
+        double acc[4][FUSED_CMAX];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int cc = 0; cc < FUSED_CMAX; cc++) acc[r][cc] = 0.0;
+        const int b0 = rg * 4;
+        for (int k = kb + lane; k < ke; k += 32) {
+            double av[4], wv[FUSED_CMAX];
+#pragma unroll
+            for (int r = 0; r < 4; r++) av[r] = (b0 + r < B) ? A[(size_t)(b0 + r) * K + k] : 0.0;
+#pragma unroll
+            for (int cc = 0; cc < FUSED_CMAX; cc++) wv[cc] = (cc < nc) ? Wc[(size_t)cc * K + k] : 0.0;
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int cc = 0; cc < FUSED_CMAX; cc++) acc[r][cc] = fma(av[r], wv[cc], acc[r][cc]);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int cc = 0; cc < FUSED_CMAX; cc++) {
+                if (cc < nc) {  // warp-uniform
+                    const double v = warp_sum_d(acc[r][cc]);
+                    if (lane == 0 && b0 + r < B) part[((size_t)ks * B + b0 + r) * FUSED_CMAX + cc] = v;
+                }
+            }
+    }
+}
+
 // issue the asynchronous fetch of the batch of step `it` (rows named by idx) into `dst`
 __device__ __forceinline__ void issue_batch_fetch(const FusedParams &p, int it, void *dst, uint64_t *mbar) {
     const int32_t *idx = p.idx + (size_t)it * p.B;
@@ -132,9 +178,12 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     double *w2t = sm + p.o_w2t;  // [d3][d2]
     double *z1o = sm + p.o_z1o;  // [B][nc0max] own pre-activations
     double *d1o = sm + p.o_d1o;  // [B][nc0max] own deltas
+    double *a1o = sm + p.o_a1o;  // [B][nc0max] own activations f(z1)
+    double *part = sm + p.o_part;  // [KS][B][4] chunk sums of the blocked dot products
+    const int KS = fused_ksplit(B, NW);
     double *z3 = sm + p.o_z3;    // [B][d3]  (reused for exp terms / loss terms)
     double *dl3 = sm + p.o_d3;   // [B][d3]
-    double *tt = sm + p.o_t;     // [B][d3]
+    double *ttbuf = sm + p.o_t;  // [2][B][d3] targets, double buffered by step parity
     double *misc = sm + p.o_misc;  // [B] row maxima / sums
     double *lut = sm + p.o_lut;  // [256] f(byte / 255.0)
     uint8_t *stage = reinterpret_cast<uint8_t *>(sm + p.o_stage);  // [B][d0] bytes
@@ -174,15 +223,33 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         double *z2pub = p.z2buf + (size_t)(it & 1) * B * d2;
 
         // ---- stage the batch: a0 = f(x) (the input layer is activated too, S:183-186) and the targets ----
-        for (int e = tid; e < B * d3; e += NT) {
-            const int b = e / d3, j = e - b * d3;
-            tt[e] = p.T ? p.T[(size_t)idx[b] * d3 + j] : ((p.labels[idx[b]] == j) ? 1.0 : 0.0);
+        // targets are double buffered: this step's were fetched during the previous step (or below for
+        // it == 0); the next step's are requested now and parked in a register until after phase 1
+        double *tt = ttbuf + (size_t)(it & 1) * B * d3, *ttn = ttbuf + (size_t)((it + 1) & 1) * B * d3;
+        if (it == 0) {
+            for (int e = tid; e < B * d3; e += NT) {
+                const int b = e / d3, j = e - b * d3;
+                tt[e] = p.T ? p.T[(size_t)idx[b] * d3 + j] : ((p.labels[idx[b]] == j) ? 1.0 : 0.0);
+            }
+        }
+        double tnext = 0.0;
+        const bool have_next = it + 1 < p.iters;
+        if (have_next && tid < B * d3) {
+            const int b = tid / d3, j = tid - b * d3;
+            const int32_t r = idx[B + b];
+            tnext = p.T ? p.T[(size_t)r * d3 + j] : ((p.labels[r] == j) ? 1.0 : 0.0);
         }
         if (p.bulk) {
             mbar_wait_parity(mbar, (uint32_t)(it & 1));
             if (u8) {
-                for (int b = warp; b < B; b += NW)
-                    for (int k = lane; k < d0; k += 32) a0[b * d0 + k] = lut[stage[b * d0 + k]];
+                // d0 % 16 == 0 here: 4 bytes per lane per iteration, two 16-byte stores
+                const uint32_t *st4 = reinterpret_cast<const uint32_t *>(stage);
+                double2 *a02 = reinterpret_cast<double2 *>(a0);
+                for (int q = tid; q < B * d0 / 4; q += NT) {
+                    const uint32_t v = st4[q];
+                    a02[2 * q] = make_double2(lut[v & 0xff], lut[(v >> 8) & 0xff]);
+                    a02[2 * q + 1] = make_double2(lut[(v >> 16) & 0xff], lut[v >> 24]);
+                }
             } else {
                 for (int b = warp; b < B; b += NW)
                     for (int k = lane; k < d0; k += 32) a0[b * d0 + k] = act(IACT, p.inner_p, a0[b * d0 + k]);
@@ -199,17 +266,23 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         if (p.bulk && u8 && tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar);
 
         // ---- phase 1: z1[:, own columns] = a0 . W0[:, own]; publish ----
-        for (int b = warp; b < B; b += NW) {
-            const double *ar = a0 + (size_t)b * d0;
-            for (int jj = 0; jj < nc0; jj++) {
-                const double *wc = w0 + (size_t)jj * d0;
-                double s0 = 0.0, s1 = 0.0;
-                int k = lane;
-                for (; k + 32 < d0; k += 64) { s0 = fma(ar[k], wc[k], s0); s1 = fma(ar[k + 32], wc[k + 32], s1); }
-                if (k < d0) s0 = fma(ar[k], wc[k], s0);
-                const double z = warp_sum_d(s0 + s1);
-                if (lane == 0) { z1o[b * ncm + jj] = z; z1pub[(size_t)b * d1 + j0 + jj] = z; }
+        blocked_dot(a0, w0, B, d0, nc0, part, warp, lane, NW);
+        if (have_next) {
+            if (tid < B * d3) ttn[tid] = tnext;
+            for (int e = NT + tid; e < B * d3; e += NT) {  // only when B*d3 exceeds the block size
+                const int b = e / d3, j = e - b * d3;
+                const int32_t r = idx[B + b];
+                ttn[e] = p.T ? p.T[(size_t)r * d3 + j] : ((p.labels[r] == j) ? 1.0 : 0.0);
             }
+        }
+        __syncthreads();
+        for (int e = tid; e < B * nc0; e += NT) {
+            const int b = e / nc0, jj = e - b * nc0;
+            double z = 0.0;
+            for (int ks = 0; ks < KS; ks++) z += part[((size_t)ks * B + b) * FUSED_CMAX + jj];
+            z1o[b * ncm + jj] = z;
+            a1o[b * ncm + jj] = act(IACT, p.inner_p, z);
+            z1pub[(size_t)b * d1 + j0 + jj] = z;
         }
         bar_target += G;
         grid_barrier(p.bar, bar_target);
@@ -230,17 +303,13 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 for (; e < n; e += NT) a1[e] = act(IACT, p.inner_p, __ldcg(z1pub + e));
             }
             __syncthreads();
-            for (int b = warp; b < B; b += NW) {
-                const double *ar = a1 + (size_t)b * d1;
-                for (int kk = 0; kk < nc1; kk++) {
-                    const double *wc = w1c + (size_t)kk * d1;
-                    double s0 = 0.0, s1 = 0.0;
-                    int j = lane;
-                    for (; j + 32 < d1; j += 64) { s0 = fma(ar[j], wc[j], s0); s1 = fma(ar[j + 32], wc[j + 32], s1); }
-                    if (j < d1) s0 = fma(ar[j], wc[j], s0);
-                    const double z = warp_sum_d(s0 + s1);
-                    if (lane == 0) z2pub[(size_t)b * d2 + k0 + kk] = z;
-                }
+            blocked_dot(a1, w1c, B, d1, nc1, part, warp, lane, NW);
+            __syncthreads();
+            for (int e = tid; e < B * nc1; e += NT) {
+                const int b = e / nc1, kk = e - b * nc1;
+                double z = 0.0;
+                for (int ks = 0; ks < KS; ks++) z += part[((size_t)ks * B + b) * FUSED_CMAX + kk];
+                z2pub[(size_t)b * d2 + k0 + kk] = z;
             }
         }
         bar_target += G;
@@ -352,16 +421,27 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
 
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
-        for (int jj = 0; jj < nc0; jj++)
-            for (int k = tid; k < d0; k += NT) {
-                double *vp = p.V0t + (size_t)(j0 + jj) * d0 + k;
-                const double vprev = *vp;
-                double g = 0.0;
-                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(d1o[b * ncm + jj], a0[(size_t)b * d0 + k]));
-                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
-                w0[jj * d0 + k] = __dsub_rn(w0[jj * d0 + k], adj);
-                *vp = adj;
+        for (int k = tid; k < d0; k += NT) {
+            double vprev[FUSED_CMAX], g[FUSED_CMAX];
+#pragma unroll
+            for (int jj = 0; jj < FUSED_CMAX; jj++) {
+                g[jj] = 0.0;
+                vprev[jj] = (jj < nc0) ? p.V0t[(size_t)(j0 + jj) * d0 + k] : 0.0;
             }
+            for (int b = 0; b < B; b++) {
+                const double a = a0[(size_t)b * d0 + k];
+#pragma unroll
+                for (int jj = 0; jj < FUSED_CMAX; jj++)
+                    g[jj] = __dadd_rn(g[jj], __dmul_rn(d1o[b * ncm + (jj < nc0 ? jj : 0)], a));
+            }
+#pragma unroll
+            for (int jj = 0; jj < FUSED_CMAX; jj++)
+                if (jj < nc0) {
+                    const double adj = sgd_adj(p.step, g[jj], B, invB, p.momentum, vprev[jj]);
+                    w0[jj * d0 + k] = __dsub_rn(w0[jj * d0 + k], adj);
+                    p.V0t[(size_t)(j0 + jj) * d0 + k] = adj;
+                }
+        }
         if (p.bulk && !u8) {
             // a0 is no longer needed: fetch the next batch's FP64 rows into it while W1 / W2 are updated
             __syncthreads();
@@ -384,10 +464,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
                 const double vprev = *vp;
                 double g = 0.0;
-                for (int b = 0; b < B; b++) {
-                    const double a = act(IACT, p.inner_p, z1o[b * ncm + jj]);
-                    g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a));
-                }
+                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a1o[b * ncm + jj]));
                 const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
                 w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
                 *vp = adj;
