@@ -4,7 +4,7 @@ The directory name carries a hyphen, so load the package through `__graft_entry_
 (registers it as module `gnn_b200`).  Importing it binds libb2nn.so; there is no CPU fallback.
 """
 from . import _capi as capi
-from . import functions
+from . import dp, functions
 from .functions import (HALF_SQUARED_ERROR, HALF_SQUARED_ERROR_PRIME, IDENTITY, IDENTITY_PRIME, LEAKY_RELU,
                         LEAKY_RELU_PRIME, RELU, RELU_PRIME, SIGMOID, SIGMOID_PRIME, TANH, TANH_PRIME,
                         ActivationFunction, ActivationPrime, LossFunction, LossFunctionPrime)

@@ -60,6 +60,9 @@ struct JavaRandom {
 
 inline int pad8(int x) { return (x + 7) & ~7; }
 
+// which tcgen05 GEMM kernel the BF16 path launches (B2NN_GEMM=0|1|2; default: CTA pair, 256x256 tile)
+enum GemmVariant { GEMM_SINGLE = 0, GEMM_PAIR_256 = 1, GEMM_PAIR_128 = 2 };
+
 // ---- per-layer state ----------------------------------------------------------------------
 struct F64Layer {
     double *w = nullptr;  // [in][out] row-major (the boundary layout, src/NeuralNet.java:30-39)
@@ -147,6 +150,7 @@ struct b2nn_net {
     int max_smem_optin = 0;
 
     // BF16 path
+    int gemm_variant = b2nn::GEMM_PAIR_256;
     bool fused_update = false;  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
     b2nn::WideBatch wb;

@@ -333,4 +333,152 @@ gemm_tn_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
 }
 
+// =====================================================================================================
+// CTA-pair variant: the same contraction with tcgen05.mma.cta_group::2.  A cluster of two CTAs (the two
+// SMs of a TPC) owns one 256 x BN tile: each CTA stages ITS 128 rows of A and ITS BN/2 rows of B, the
+// leader's single MMA thread drives both tensor cores (M = 256), and each CTA's TMEM receives its 128
+// accumulator rows.  Per-SM shared-memory read traffic per MMA drops from A+B to A+B/2 and the smem
+// ring deepens (6-8 stages).  Barrier topology:
+//   full[s]    leader only, 1 arrival (its expect_tx of BOTH CTAs' bytes); both CTAs' TMA credit it
+//   empty[s]   one per CTA, signalled in both CTAs by the multicast tcgen05.commit
+//   tfull[a]   one per CTA, multicast commit -> each CTA's epilogue warps
+//   tempty[a]  leader only, 8 arrivals (4 epilogue warps of each CTA, the peer's arrive remotely)
+template <int BN>
+struct PairCfg {
+    static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;         // 16 KB: this CTA's 128 rows
+    static constexpr int B_BYTES = (BN / 2) * GEMM_BK * 2;        // this CTA's half of the B tile
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (192 * 1024) / STAGE_BYTES;     // 6 (BN=256) or 8 (BN=128)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr uint32_t TMEM_COLS = 2 * BN;                 // double-buffered accumulator
+};
+
+template <int EPI, int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tn_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const GemmArgs g) {
+    using Cfg = PairCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t *smem_a = smem;
+    uint8_t *smem_b = smem + Cfg::STAGES * Cfg::A_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+    uint64_t *full_bar = bars;
+    uint64_t *empty_bar = bars + Cfg::STAGES;
+    uint64_t *tfull_bar = bars + 2 * Cfg::STAGES;
+    uint64_t *tempty_bar = bars + 2 * Cfg::STAGES + 2;
+    uint32_t *tmem_base_slot = reinterpret_cast<uint32_t *>(bars + 2 * Cfg::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+    const int m_tiles = (g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
+    const int n_tiles = (g.N + BN - 1) / BN;
+    const int num_tiles = m_tiles * n_tiles;
+    const int k_blocks = (g.K + GEMM_BK - 1) / GEMM_BK;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+        for (int s = 0; s < Cfg::STAGES; s++) {
+            ptx::mbar_init(&full_bar[s], 1);
+            ptx::mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < 2; a++) {
+            ptx::mbar_init(&tfull_bar[a], 1);
+            ptx::mbar_init(&tempty_bar[a], 8);
+        }
+        ptx::fence_barrier_init();
+    }
+    ptx::cluster_sync();  // both CTAs' barriers exist before anyone signals across the pair
+    if (warp == 1) {
+        ptx::tmem_alloc_pair(tmem_base_slot, Cfg::TMEM_COLS);
+        ptx::tmem_relinquish_pair();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs) {
+                const int m0 = (t / n_tiles) * (2 * GEMM_BM) + (int)rank * GEMM_BM;
+                const int n0 = (t % n_tiles) * BN + (int)rank * (BN / 2);
+                for (int kb = 0; kb < k_blocks; kb++) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                    ptx::tma_load_2d_pair(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * GEMM_BK, m0);
+                    ptx::tma_load_2d_pair(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * GEMM_BK, n0);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (rank == 0 && lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * GEMM_BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs) {
+                ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
+                for (int kb = 0; kb < k_blocks; kb++) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t da = ptx::make_desc_kmajor_sw128(ptx::smem_u32(smem_a + stage * Cfg::A_BYTES));
+                    const uint64_t db = ptx::make_desc_kmajor_sw128(ptx::smem_u32(smem_b + stage * Cfg::B_BYTES));
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; k++)
+                        ptx::mma_f16_ss_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                                             (kb | k) != 0 ? 1u : 0u);
+                    ptx::mma_commit_pair(&empty_bar[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::mma_commit_pair(&tfull_bar[acc]);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps (2..5), each CTA drains its own 128 rows ==========
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int t = pair; t < num_tiles; t += num_pairs) {
+            const int m0 = (t / n_tiles) * (2 * GEMM_BM) + (int)rank * GEMM_BM;
+            const int n0 = (t % n_tiles) * BN;
+            ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+            ptx::tc_fence_after();
+            const int m = m0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * BN;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t r[32];
+                ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
+                ptx::tmem_ld_wait();
+                epilogue_chunk<EPI>(g, m, n0 + c0, r);
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_leader(&tempty_bar[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync();  // the peer may still read this CTA's smem / signal its barriers until here
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
 }  // namespace b2nn

@@ -63,6 +63,20 @@ int profile_flush(b2nn_net *net) {
     return B2NN_OK;
 }
 
+template <int EPI, int BN>
+static int launch_pair(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_bf16_pair_kernel<EPI, BN>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<BN>::SMEM_BYTES));
+        attr_done = true;
+    }
+    const int tiles = ((g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((g.N + BN - 1) / BN);
+    const int pairs = tiles < net->num_sms / 2 ? tiles : net->num_sms / 2;
+    gemm_tn_bf16_pair_kernel<EPI, BN><<<2 * pairs, GEMM_THREADS, PairCfg<BN>::SMEM_BYTES, net->stream>>>(ta, tb, g);
+    return B2NN_OK;
+}
+
 template <int EPI>
 static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
     static bool attr_done = false;
@@ -71,8 +85,6 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
                                            GEMM_SMEM_BYTES));
         attr_done = true;
     }
-    const int tiles = ((g.M + GEMM_BM - 1) / GEMM_BM) * ((g.N + GEMM_BN - 1) / GEMM_BN);
-    const int grid = tiles < net->num_sms ? tiles : net->num_sms;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (net->profiling) {
         if (net->prof_used + 2 > net->prof_events.size()) B2_TRY(profile_flush(net));
@@ -80,7 +92,15 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
         e1 = net->prof_events[net->prof_used++];
         B2_CHECK_CUDA(cudaEventRecord(e0, net->stream));
     }
-    gemm_tn_bf16_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
+    if (net->gemm_variant == GEMM_PAIR_256) {
+        B2_TRY((launch_pair<EPI, 256>(net, ta, tb, g)));
+    } else if (net->gemm_variant == GEMM_PAIR_128) {
+        B2_TRY((launch_pair<EPI, 128>(net, ta, tb, g)));
+    } else {
+        const int tiles = ((g.M + GEMM_BM - 1) / GEMM_BM) * ((g.N + GEMM_BN - 1) / GEMM_BN);
+        const int grid = tiles < net->num_sms ? tiles : net->num_sms;
+        gemm_tn_bf16_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
+    }
     if (net->profiling) {
         B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
         net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
@@ -88,6 +108,11 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
+}
+
+// rows of the B-operand TMA box for the net's GEMM variant (A boxes are always 128 rows)
+int wide_b_box(const b2nn_net *net) {
+    return net->gemm_variant == GEMM_PAIR_256 ? 128 : net->gemm_variant == GEMM_PAIR_128 ? 64 : GEMM_BN;
 }
 
 int wide_gemm_raw(b2nn_net *net, int epi, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
@@ -161,8 +186,8 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
             B2_CHECK_CUDA(cudaMalloc(&y.g, nf * sizeof(float)));
             B2_CHECK_CUDA(cudaMemset(y.g, 0, nf * sizeof(float)));
         }
-        B2_TRY(make_tmap_bf16(&y.tm_wt, y.wt, y.in, y.out, y.ld_t, GEMM_BN));  // forward: N=out, K=in
-        B2_TRY(make_tmap_bf16(&y.tm_wn, y.wn, y.out, y.in, y.ld_n, GEMM_BN));  // delta:   N=in,  K=out
+        B2_TRY(make_tmap_bf16(&y.tm_wt, y.wt, y.in, y.out, y.ld_t, wide_b_box(net)));  // forward: N=out, K=in
+        B2_TRY(make_tmap_bf16(&y.tm_wn, y.wn, y.out, y.in, y.ld_n, wide_b_box(net)));  // delta:   N=in,  K=out
     }
     return wide_upload_weights(net, w_host.data(), false);
 }
@@ -210,7 +235,7 @@ int wide_ensure_batch(b2nn_net *net, int B) {
             B2_CHECK_CUDA(cudaMalloc(&b.dt[l], (size_t)dl * b.ldB * 2));
             B2_CHECK_CUDA(cudaMemset(b.dt[l], 0, (size_t)dl * b.ldB * 2));
             B2_TRY(make_tmap_bf16(&b.tm_d[l], b.d[l], dl, B, ld, GEMM_BM));       // delta A: M=B, K=d_l
-            B2_TRY(make_tmap_bf16(&b.tm_dt[l], b.dt[l], B, dl, b.ldB, GEMM_BN));  // gradient B: N=d_l, K=B
+            B2_TRY(make_tmap_bf16(&b.tm_dt[l], b.dt[l], B, dl, b.ldB, wide_b_box(net)));  // gradient B: N=d_l, K=B
         }
     }
     const int ldL = pad8(net->dims[L]);

@@ -1,0 +1,100 @@
+"""Worker bodies for the multi-process tests (spawned by test_dp.py).  The CPU (gloo) worker checks
+the data-parallel HOST logic against the oracle; the GPU (nccl) worker checks the CUDA path."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _init(rank, world, port, backend):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    return dist
+
+
+def gloo_worker(rank, world, port, out_dir):
+    """Every rank draws the same global index lists, takes its slice (dp.shard_index_lists), sums the
+    oracle's per-sample gradients over the slice, all-reduces the sums over gloo and applies the
+    reference's update with the GLOBAL batch size; rank 0 stores the result for the parent to compare
+    with a single-process oracle run."""
+    import torch
+    import __graft_entry__ as ge
+    from oracle import oracle as orc
+    dist = _init(rank, world, port, "gloo")
+    g = ge.load_package()
+    dims, n_rows, gB, iters, step, mu = [12, 9, 7, 4], 64, 8, 5, 0.05, 0.9
+    rng = np.random.RandomState(7)
+    x = rng.rand(n_rows, dims[0])
+    lab = rng.randint(0, dims[-1], n_rows)
+    t = np.zeros((n_rows, dims[-1]))
+    t[np.arange(n_rows), lab] = 1.0
+    idx = g.Sampler(n_rows, seed=1).draw(iters, gB)          # identical on every rank
+    mine = g.dp.shard_index_lists(idx, rank, world)
+    # the slices tile the global batch exactly
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine.tolist())
+    assert np.array_equal(np.concatenate([np.asarray(a) for a in gathered], axis=1), idx)
+
+    net = orc.OracleNet(dims)
+    w, v = net.get_weights(), np.zeros(net.get_weights().size)
+    for it in range(iters):
+        net.set_weights(w)
+        gsum = np.zeros_like(w)
+        for r in mine[it]:
+            gsum += net.weight_gradient(x[r], t[r])
+        tg = torch.from_numpy(gsum)
+        dist.all_reduce(tg)                                    # the cross-GPU batch sum
+        v = step * tg.numpy() / gB + mu * v                    # S:333, divide by the GLOBAL batch
+        w = w - v
+    if rank == 0:
+        np.save(os.path.join(out_dir, "dp_w.npy"), w)
+        np.save(os.path.join(out_dir, "dp_idx.npy"), idx)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def nccl_worker(rank, world, port, out_dir):
+    """BF16 nets, one per GPU, stepping on their slice of each global batch with the per-layer NCCL
+    all-reduce inside libb2nn.so; rank 0 also steps an un-sharded net on the whole global batch."""
+    import torch
+    import __graft_entry__ as ge
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    g = ge.load_package()
+    dims, gB, iters, step, mu = [256, 384, 128, 40], 256 * world, 6, 0.05, 0.9
+    flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX
+    rng = np.random.RandomState(11)
+    n_rows = 4 * gB
+    x = rng.rand(n_rows, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], n_rows).astype(np.int32)
+    idx = g.Sampler(n_rows, seed=1).draw(iters, gB)
+    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+                                         flags=flags, device=rank)
+    g.dp.init_comm(net, dist)
+    mine = g.dp.shard_index_lists(idx, rank, world)
+    for it in range(iters):
+        net.gradientStepLabeled(x[mine[it]], lab[mine[it]], step, mu)
+    w = net.getWeights()
+    # every replica must hold the same weights bit for bit (same all-reduced gradient, same update)
+    tw = torch.from_numpy(w).cuda()
+    ref = tw.clone()
+    dist.broadcast(ref, src=0)
+    same = bool(torch.equal(tw, ref))
+    flag = torch.tensor([1 if same else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        single = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+                                                flags=flags, device=0)
+        w0 = single.getWeights()
+        for it in range(iters):
+            single.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu)
+        np.savez(os.path.join(out_dir, "nccl.npz"), w_dp=w, w_single=single.getWeights(), w0=w0,
+                 replicas_equal=int(flag.item()), launches=net.kernelLaunches())
+    dist.barrier()
+    dist.destroy_process_group()
