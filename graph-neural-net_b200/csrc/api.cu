@@ -83,8 +83,6 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     {
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = fu != nullptr && fu[0] == '1';
-        const char *gv = getenv("B2NN_GEMM");
-        if (gv != nullptr && gv[0] >= '0' && gv[0] <= '2') net->gemm_variant = gv[0] - '0';
         const char *ff = getenv("B2NN_F64_FUSED");
         net->fused_f64_disabled = ff != nullptr && ff[0] == '0';
         net->coop_launch = prop.cooperativeLaunch != 0;

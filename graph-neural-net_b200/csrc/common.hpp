@@ -60,8 +60,6 @@ struct JavaRandom {
 
 inline int pad8(int x) { return (x + 7) & ~7; }
 
-// which tcgen05 GEMM kernel the BF16 path launches (B2NN_GEMM=0|1|2; default: CTA pair, 256x256 tile)
-enum GemmVariant { GEMM_SINGLE = 0, GEMM_PAIR_256 = 1, GEMM_PAIR_128 = 2 };
 
 // ---- per-layer state ----------------------------------------------------------------------
 struct F64Layer {
@@ -71,29 +69,25 @@ struct F64Layer {
 
 struct WideLayer {
     int in = 0, out = 0;
-    int ld_n = 0;               // pad8(out): leading dim of [in][out] arrays
-    int ld_t = 0;               // pad8(in):  leading dim of [out][in] arrays
+    int ld_n = 0;               // pad8(out): leading dim of the [in][out] arrays
     float *w = nullptr;         // FP32 master [in][ld_n]
     float *v = nullptr;         // FP32 velocity [in][ld_n]
-    float *g = nullptr;         // FP32 gradient [in][ld_n] (data-parallel only)
-    __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]  : B operand of the delta GEMM (N=in, K=out)
-    __nv_bfloat16 *wt = nullptr;  // BF16 [out][ld_t] : B operand of the forward GEMM (N=out, K=in)
-    CUtensorMap tm_wt, tm_wn;     // B-operand maps (box 256 x 64)
+    float *g = nullptr;         // FP32 summed gradient [in][ld_n]
+    __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]: GEMM operand copy (MN-major B forward, K-major B delta)
+    CUtensorMap tm_w;             // 64 x 64 box map over wn
 };
 
-// activations / deltas for one batch size
+// activations / deltas for one batch size (row-major only; the GEMMs read either major-ness)
 struct WideBatch {
-    int B = 0, ldB = 0;
+    int B = 0;
     std::vector<__nv_bfloat16 *> a;    // a[l]  [B][pad8(d_l)]   l = 0..L-1 (activations incl. f(x))
-    std::vector<__nv_bfloat16 *> at;   // at[l] [d_l][ldB]
     std::vector<__nv_bfloat16 *> d;    // d[l]  [B][pad8(d_l)]   l = 1..L   (deltas)
-    std::vector<__nv_bfloat16 *> dt;   // dt[l] [d_l][ldB]
     float *logits = nullptr;           // [B][pad8(d_L)] FP32
     float *row_loss = nullptr;         // [B]
     int32_t *labels = nullptr;         // [B]
     float *tdense = nullptr;           // [B][pad8(d_L)] FP32 dense targets (optional path)
     void *xstage = nullptr;            // staged raw input rows [B][d0] (any dtype, 8 B / element max)
-    std::vector<CUtensorMap> tm_a, tm_at, tm_d, tm_dt;  // A-operand maps (box 128 x 64)
+    std::vector<CUtensorMap> tm_a, tm_d;  // 64 x 64 box maps over a[l], d[l]
     double *loss_sum = nullptr;        // device scalar(s)
 };
 
@@ -150,7 +144,6 @@ struct b2nn_net {
     int max_smem_optin = 0;
 
     // BF16 path
-    int gemm_variant = b2nn::GEMM_PAIR_256;
     bool fused_update = false;  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
     b2nn::WideBatch wb;

@@ -198,12 +198,26 @@ __device__ __forceinline__ uint64_t make_desc_kmajor_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
     return d;
 }
-// Instruction descriptor, kind::f16: BF16 x BF16 -> FP32, both operands K-major.
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n) {
+// Shared-memory matrix descriptor for an MN-major operand tile (the M or N index is the contiguous
+// one in memory) staged by TMA as 64-element x 64-row boxes with CU_TENSOR_MAP_SWIZZLE_128B: each box is
+// 64 K-rows of 128 B (= 64 MN elements); 8-row groups 1024 B apart along K (SBO); successive 64-element
+// MN chunks `chunk_bytes` apart (LBO).  Canonical form ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16 B units.
+__device__ __forceinline__ uint64_t make_desc_mnmajor_sw128(uint32_t smem_addr, uint32_t chunk_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((chunk_bytes >> 4) & 0x3FFF) << 16;  // leading byte offset: next 64 MN elements
+    d |= (uint64_t)(1024 >> 4) << 32;                    // stride byte offset: next 8 K rows
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// Instruction descriptor, kind::f16: BF16 x BF16 -> FP32; a_mn / b_mn select MN-major operands.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n, bool a_mn = false, bool b_mn = false) {
     return (1u << 4)                      // D format F32
            | (1u << 7)                    // A format BF16
            | (1u << 10)                   // B format BF16
-           | (0u << 15) | (0u << 16)      // A, B K-major
+           | ((a_mn ? 1u : 0u) << 15)     // A major: 0 = K, 1 = MN
+           | ((b_mn ? 1u : 0u) << 16)     // B major
            | ((uint32_t)(n >> 3) << 17)   // N / 8
            | ((uint32_t)(m >> 4) << 24);  // M / 16
 }

@@ -1,9 +1,8 @@
 // wide_kernels.cuh -- the HBM-bound kernels around the tcgen05 GEMMs of the BF16 path:
 // input prologue (K8), fused softmax-cross-entropy gradient (K5) / general output delta (K6),
 // momentum-SGD update for the data-parallel case (K7) and the evaluation row pass.
-// All of them read each input once, write row-major AND transposed BF16 copies through a
-// 32x32 shared-memory tile (both global accesses coalesced), and are sized by the caller as
-// plain grids over 32-row / 32x32 tiles.
+// All of them read each input once and write each output once, row-major, with 16-byte accesses
+// where the shapes allow (the GEMMs read either major-ness, so no transposed copies are written).
 #pragma once
 #include <cuda_bf16.h>
 
@@ -24,32 +23,32 @@ template <>
 __device__ __forceinline__ float load_as_float<__nv_bfloat16>(const __nv_bfloat16 *p) { return __bfloat162float(*p); }
 
 // a0 = f(x) (the reference activates the INPUT layer too, SoftmaxCrossEntropyNeuralNet.java:183-186)
-// for the rows named by idx (or rows 0..B-1), cast to BF16, stored [B][ld_a] and transposed [d0][ldB].
+// for the rows named by idx (or rows 0..B-1), cast to BF16, stored [B][ld_a].
 // X may live in HBM or in mapped pinned host memory (then this kernel IS the host->device copy).
-// grid (ceil(d0/32), ceil(B/32)), block (32, 8)
+// One thread per 8 consecutive elements of a row (one 16-byte store); grid-stride over B * ceil(d0/8).
 template <typename T>
-__global__ void input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, int d0, int act,
-                               float act_param, __nv_bfloat16 *__restrict__ a, int ld_a,
-                               __nv_bfloat16 *__restrict__ at, int ldB) {
-    __shared__ float tile[32][33];
-    const int i0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
-    const int tx = threadIdx.x, ty = threadIdx.y;
+__global__ void __launch_bounds__(256)
+input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, int d0, int act, float act_param,
+               __nv_bfloat16 *__restrict__ a, int ld_a) {
+    const int groups = (d0 + 7) >> 3;
+    const long long total = (long long)B * groups;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(t / groups), i0 = (int)(t % groups) * 8;
+        const long long src = idx ? idx[b] : b;
+        const T *x = X + src * d0 + i0;
+        __nv_bfloat16 *o = a + (size_t)b * ld_a + i0;
+        if (i0 + 8 <= d0) {
+            float v[8];
 #pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int b = b0 + r, i = i0 + tx;
-        float v = 0.f;
-        if (b < B && i < d0) {
-            const long long src = idx ? idx[b] : b;
-            v = act_apply(act, act_param, load_as_float<T>(X + src * d0 + i));
-            a[(size_t)b * ld_a + i] = __float2bfloat16_rn(v);
+            for (int e = 0; e < 8; e++) v[e] = act_apply(act, act_param, load_as_float<T>(x + e));
+            uint4 u;
+            u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+            u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4 *>(o) = u;
+        } else {
+            for (int e = 0; i0 + e < d0; e++) o[e] = __float2bfloat16_rn(act_apply(act, act_param, load_as_float<T>(x + e)));
         }
-        tile[r][tx] = v;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int i = i0 + r, b = b0 + tx;
-        if (i < d0 && b < B) at[(size_t)i * ldB + b] = __float2bfloat16_rn(tile[tx][r]);
     }
 }
 
@@ -64,76 +63,61 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// Output layer of the BF16 path.  One block = 32 batch rows, 256 threads (8 warps x 4 rows).
+// Output layer of the BF16 path.  One warp per batch row (8 rows per block); the row of logits is read
+// from HBM once and re-read from L1.
 //  kind 0: p = softmax(z) (max-subtracted: identical maths, SoftmaxCrossEntropyNeuralNet.java:357-376),
 //          loss = -sum t log p (:213-217), delta = p - t (:249-251); t one-hot from labels or dense.
 //  kind 1: a = f_last(z); loss = sum L(a,t); delta = L'(a,t) f_last'(z) (GeneralNeuralNet.java:236-239,268-271).
-// Writes delta as BF16 row-major d[B][ld_d] and transposed dt[dL][ldB]; row_loss[B] FP32.
+// Writes delta as BF16 d[B][ld_d]; row_loss[B] FP32.
 __global__ void __launch_bounds__(256)
 output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ labels,
              const float *__restrict__ tdense, int ld_t, int B, int dL, int kind, int last_act, float last_param,
-             __nv_bfloat16 *__restrict__ d, int ld_d, __nv_bfloat16 *__restrict__ dt, int ldB,
-             float *__restrict__ row_loss) {
-    __shared__ float s_max[32], s_inv[32], s_lse[32];
-    __shared__ float tile[32][33];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b0 = blockIdx.x * 32;
+             __nv_bfloat16 *__restrict__ d, int ld_d, float *__restrict__ row_loss) {
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (b >= B) return;
+    const float *z = Z + (size_t)b * ld_z;
+    const float *t = tdense ? tdense + (size_t)b * ld_t : nullptr;
+    const int lab = labels ? labels[b] : -1;
+    __nv_bfloat16 *drow = d + (size_t)b * ld_d;
+    float mx = 0.f, inv = 1.f, lse = 0.f;
     if (kind == 0) {
-        for (int rr = 0; rr < 4; rr++) {
-            const int r = warp * 4 + rr, b = b0 + r;
-            float mx = -INFINITY, sum = 0.f;
-            if (b < B) {
-                const float *z = Z + (size_t)b * ld_z;
-                for (int c = lane; c < dL; c += 32) mx = fmaxf(mx, z[c]);
-                mx = warp_max(mx);
-                for (int c = lane; c < dL; c += 32) sum += __expf(z[c] - mx);
-                sum = warp_sum(sum);
-            }
-            if (lane == 0) { s_max[r] = mx; s_inv[r] = 1.f / sum; s_lse[r] = __logf(sum); }
-        }
+        mx = -INFINITY;
+        for (int c = lane; c < dL; c += 32) mx = fmaxf(mx, z[c]);
+        mx = warp_max(mx);
+        float sum = 0.f;
+        for (int c = lane; c < dL; c += 32) sum += __expf(z[c] - mx);
+        sum = warp_sum(sum);
+        inv = 1.f / sum;
+        lse = __logf(sum);
     }
-    __syncthreads();
-    float lacc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int c0 = 0; c0 < dL; c0 += 32) {
-        const int c = c0 + lane;
+    float lacc = 0.f;
+    // two columns per lane per step -> 4-byte stores, 128 B per warp
+    for (int c0 = 2 * lane; c0 < dL; c0 += 64) {
+        float dv[2] = {0.f, 0.f};
 #pragma unroll
-        for (int rr = 0; rr < 4; rr++) {
-            const int r = warp * 4 + rr, b = b0 + r;
-            float dv = 0.f;
-            if (b < B && c < dL) {
-                const float z = Z[(size_t)b * ld_z + c];
-                float t;
-                if (tdense) t = tdense[(size_t)b * ld_t + c];
-                else t = (labels[b] == c) ? 1.f : 0.f;
+        for (int e = 0; e < 2; e++) {
+            const int c = c0 + e;
+            if (c < dL) {
+                const float zc = z[c];
+                const float tc = t ? t[c] : ((c == lab) ? 1.f : 0.f);
                 if (kind == 0) {
-                    const float zs = z - s_max[r];
-                    const float p = __expf(zs) * s_inv[r];
-                    dv = p - t;
-                    if (t != 0.f) lacc[rr] -= t * (zs - s_lse[r]);  // -t log p
+                    const float zs = zc - mx;
+                    dv[e] = __expf(zs) * inv - tc;
+                    if (tc != 0.f) lacc -= tc * (zs - lse);  // -t log p
                 } else {
-                    const float a = act_apply(last_act, last_param, z);
-                    const float diff = a - t;  // half squared error: L = 0.5 diff^2, L' = diff
-                    lacc[rr] += 0.5f * diff * diff;
-                    dv = diff * act_prime_from_a(last_act, last_param, a);
+                    const float a = act_apply(last_act, last_param, zc);
+                    const float diff = a - tc;  // half squared error: L = 0.5 diff^2, L' = diff
+                    lacc += 0.5f * diff * diff;
+                    dv[e] = diff * act_prime_from_a(last_act, last_param, a);
                 }
-                d[(size_t)b * ld_d + c] = __float2bfloat16_rn(dv);
             }
-            tile[r][lane] = dv;
         }
-        __syncthreads();
-#pragma unroll
-        for (int rr = 0; rr < 4; rr++) {
-            const int cc = c0 + warp * 4 + rr, b = b0 + lane;
-            if (cc < dL && b < B) dt[(size_t)cc * ldB + b] = __float2bfloat16_rn(tile[lane][warp * 4 + rr]);
-        }
-        __syncthreads();
+        if (c0 + 1 < dL) *reinterpret_cast<uint32_t *>(drow + c0) = pack_bf16x2(dv[0], dv[1]);
+        else drow[c0] = __float2bfloat16_rn(dv[0]);
     }
-#pragma unroll
-    for (int rr = 0; rr < 4; rr++) {
-        const float l = warp_sum(lacc[rr]);
-        const int b = b0 + warp * 4 + rr;
-        if (lane == 0 && b < B && row_loss) row_loss[b] = l;
-    }
+    lacc = warp_sum(lacc);
+    if (lane == 0 && row_loss) row_loss[b] = lacc;
 }
 
 // Evaluation row pass: one warp per row.  `>=` argmax so the LAST maximal index wins
@@ -180,38 +164,25 @@ __global__ void eval_rows(const float *__restrict__ Z, int ld_z, const int32_t *
     }
 }
 
-// Momentum-SGD update after the gradient all-reduce (SoftmaxCrossEntropyNeuralNet.java:325-342):
-// v = scale*g + mu*v ; w -= v ; emit BF16 w row-major [in][ld_n] and transposed [out][ld_t].
-// cast_only: just (re)build the BF16 copies from the master weights.
-// grid (ceil(out/32), ceil(in/32)), block (32, 8)
-__global__ void sgd_update(const float *__restrict__ g, float *__restrict__ w, float *__restrict__ v, int in,
-                           int out, int ld_n, float scale, float momentum, int cast_only,
-                           __nv_bfloat16 *__restrict__ wn, __nv_bfloat16 *__restrict__ wt, int ld_t) {
-    __shared__ float tile[32][33];
-    const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
-    const int tx = threadIdx.x, ty = threadIdx.y;
-#pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int i = i0 + r, j = j0 + tx;
-        float wv = 0.f;
-        if (i < in && j < out) {
-            const size_t o = (size_t)i * ld_n + j;
-            wv = w[o];
-            if (!cast_only) {
-                const float vn = scale * g[o] + momentum * v[o];
-                wv -= vn;
-                v[o] = vn;
-                w[o] = wv;
-            }
-            wn[o] = __float2bfloat16_rn(wv);
+// Momentum-SGD update (SoftmaxCrossEntropyNeuralNet.java:325-342) over the padded [in][ld_n] arrays as one
+// flat stream of float4: v = scale*g + mu*v ; w -= v ; emit the BF16 operand copy wn.  Algorithmic traffic
+// 12 B read + 10 B written per parameter.  cast_only: just (re)build wn from the master weights.
+__global__ void __launch_bounds__(256)
+sgd_update(const float4 *__restrict__ g, float4 *__restrict__ w, float4 *__restrict__ v, long long n4, float scale,
+           float momentum, int cast_only, uint2 *__restrict__ wn) {
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n4;
+         q += (long long)gridDim.x * blockDim.x) {
+        float4 wv = w[q];
+        if (!cast_only) {
+            const float4 gv = __ldcs(g + q);  // the gradient is dead after this read
+            float4 vv = v[q];
+            vv.x = scale * gv.x + momentum * vv.x; vv.y = scale * gv.y + momentum * vv.y;
+            vv.z = scale * gv.z + momentum * vv.z; vv.w = scale * gv.w + momentum * vv.w;
+            wv.x -= vv.x; wv.y -= vv.y; wv.z -= vv.z; wv.w -= vv.w;
+            v[q] = vv;
+            w[q] = wv;
         }
-        tile[r][tx] = wv;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int j = j0 + r, i = i0 + tx;
-        if (j < out && i < in) wt[(size_t)j * ld_t + i] = __float2bfloat16_rn(tile[tx][r]);
+        wn[q] = make_uint2(pack_bf16x2(wv.x, wv.y), pack_bf16x2(wv.z, wv.w));
     }
 }
 

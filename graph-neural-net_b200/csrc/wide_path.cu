@@ -1,11 +1,11 @@
 // wide_path.cu -- host orchestration of the BF16 tensor-core path: per-step sequence of
 // tcgen05 GEMMs (gemm_tcgen05.cuh) and the HBM-bound kernels around them (wide_kernels.cuh).
 // Data layout in HBM (per layer l with W_l: d_l x d_{l+1}):
-//   w, v   FP32 [d_l][pad8(d_{l+1})]           master weights / velocity (boundary layout, padded)
-//   wn     BF16 [d_l][pad8(d_{l+1})]           K-major B operand of the delta GEMM
-//   wt     BF16 [d_{l+1}][pad8(d_l)]           K-major B operand of the forward GEMM
-//   a[l]   BF16 [B][pad8(d_l)], at[l] [d_l][pad8(B)]     activations (+ transposed for the gradient GEMM)
-//   d[l]   BF16 [B][pad8(d_l)], dt[l] [d_l][pad8(B)]     deltas      (+ transposed)
+//   w, v, g  FP32 [d_l][pad8(d_{l+1})]   master weights / velocity / summed gradient (boundary layout, padded)
+//   wn       BF16 [d_l][pad8(d_{l+1})]   the GEMM operand copy of w (MN-major B forward, K-major B delta)
+//   a[l]     BF16 [B][pad8(d_l)]         activations (K-major A forward, MN-major A gradient)
+//   d[l]     BF16 [B][pad8(d_l)]         deltas      (K-major A delta,   MN-major B gradient)
+// No transposed copies exist: UMMA reads either major-ness from the same row-major buffer.
 #include "wide_path.hpp"
 
 #include "comm.hpp"
@@ -31,20 +31,20 @@ static PFN_tmapEncodeTiled get_encode_fn() {
     return fn;
 }
 
-// K-major BF16 operand: global [rows][ld] with `k` valid elements per row; box = box_rows x 64,
-// 128-byte swizzle (matches make_desc_kmajor_sw128), out-of-bounds elements read as zero.
-int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t k, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+// One map per BF16 buffer [rows][ld] with `inner` valid elements per row: 64 x 64 box, 128-byte swizzle
+// (matches make_desc_kmajor_sw128 / make_desc_mnmajor_sw128), out-of-bounds elements read as zero.
+int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld) {
     PFN_tmapEncodeTiled fn = get_encode_fn();
     B2_REQUIRE(fn != nullptr, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-    cuuint64_t gdim[2] = {k, rows};
+    cuuint64_t gdim[2] = {inner, rows};
     cuuint64_t gstride[1] = {ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, box_rows};
+    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, 64};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    B2_REQUIRE(r == CUDA_SUCCESS, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (k=%llu rows=%llu ld=%llu)",
-               (int)r, (unsigned long long)k, (unsigned long long)rows, (unsigned long long)ld);
+    B2_REQUIRE(r == CUDA_SUCCESS, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (inner=%llu rows=%llu ld=%llu)",
+               (int)r, (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)ld);
     return B2NN_OK;
 }
 
@@ -63,26 +63,12 @@ int profile_flush(b2nn_net *net) {
     return B2NN_OK;
 }
 
-template <int EPI, int BN>
-static int launch_pair(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_bf16_pair_kernel<EPI, BN>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<BN>::SMEM_BYTES));
-        attr_done = true;
-    }
-    const int tiles = ((g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((g.N + BN - 1) / BN);
-    const int pairs = tiles < net->num_sms / 2 ? tiles : net->num_sms / 2;
-    gemm_tn_bf16_pair_kernel<EPI, BN><<<2 * pairs, GEMM_THREADS, PairCfg<BN>::SMEM_BYTES, net->stream>>>(ta, tb, g);
-    return B2NN_OK;
-}
-
-template <int EPI>
+template <int EPI, bool A_MN, bool B_MN>
 static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
     static bool attr_done = false;
     if (!attr_done) {
-        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_bf16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           GEMM_SMEM_BYTES));
+        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_pair_kernel<EPI, A_MN, B_MN>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
         attr_done = true;
     }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -92,15 +78,10 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
         e1 = net->prof_events[net->prof_used++];
         B2_CHECK_CUDA(cudaEventRecord(e0, net->stream));
     }
-    if (net->gemm_variant == GEMM_PAIR_256) {
-        B2_TRY((launch_pair<EPI, 256>(net, ta, tb, g)));
-    } else if (net->gemm_variant == GEMM_PAIR_128) {
-        B2_TRY((launch_pair<EPI, 128>(net, ta, tb, g)));
-    } else {
-        const int tiles = ((g.M + GEMM_BM - 1) / GEMM_BM) * ((g.N + GEMM_BN - 1) / GEMM_BN);
-        const int grid = tiles < net->num_sms ? tiles : net->num_sms;
-        gemm_tn_bf16_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
-    }
+    const int tiles = ((g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((g.N + GEMM_BN - 1) / GEMM_BN);
+    const int max_pairs = net->num_sms / 2;
+    const int pairs = tiles < max_pairs ? tiles : max_pairs;
+    gemm_bf16_pair_kernel<EPI, A_MN, B_MN><<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
     if (net->profiling) {
         B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
         net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
@@ -110,26 +91,13 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     return B2NN_OK;
 }
 
-// rows of the B-operand TMA box for the net's GEMM variant (A boxes are always 128 rows)
-int wide_b_box(const b2nn_net *net) {
-    return net->gemm_variant == GEMM_PAIR_256 ? 128 : net->gemm_variant == GEMM_PAIR_128 ? 64 : GEMM_BN;
-}
-
-int wide_gemm_raw(b2nn_net *net, int epi, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
-    switch (epi) {
-    case EPI_ACT: return launch_gemm<EPI_ACT>(net, ta, tb, g);
-    case EPI_LOGITS: return launch_gemm<EPI_LOGITS>(net, ta, tb, g);
-    case EPI_DX: return launch_gemm<EPI_DX>(net, ta, tb, g);
-    case EPI_DW_UPDATE: return launch_gemm<EPI_DW_UPDATE>(net, ta, tb, g);
-    default: return launch_gemm<EPI_DW_STORE>(net, ta, tb, g);
-    }
-}
-
-static int rebuild_bf16_copies(b2nn_net *net, int l) {
-    WideLayer &y = net->wide[l];
-    dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
-    wide::sgd_update<<<grid, block, 0, net->stream>>>(nullptr, y.w, y.v, y.in, y.out, y.ld_n, 0.f, 0.f, 1, y.wn,
-                                                       y.wt, y.ld_t);
+static int launch_update(b2nn_net *net, WideLayer &y, float scale, float momentum, int cast_only, cudaStream_t st) {
+    const long long n4 = (long long)y.in * y.ld_n / 4;
+    long long blocks = (n4 + 255) / 256;
+    const long long cap = (long long)net->num_sms * 8;
+    if (blocks > cap) blocks = cap;
+    wide::sgd_update<<<(int)blocks, 256, 0, st>>>((const float4 *)y.g, (float4 *)y.w, (float4 *)y.v, n4, scale,
+                                                  momentum, cast_only, (uint2 *)y.wn);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -146,7 +114,7 @@ int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity) {
         B2_CHECK_CUDA(cudaMemcpyAsync(velocity ? y.v : y.w, tmp.data(), tmp.size() * sizeof(float),
                                       cudaMemcpyHostToDevice, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
-        if (!velocity) B2_TRY(rebuild_bf16_copies(net, l));
+        if (!velocity) B2_TRY(launch_update(net, y, 0.f, 0.f, 1, net->stream));
     }
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     return B2NN_OK;
@@ -173,21 +141,18 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
         y.in = net->dims[l]; y.out = net->dims[l + 1];
-        y.ld_n = pad8(y.out); y.ld_t = pad8(y.in);
+        y.ld_n = pad8(y.out);
         const size_t nf = (size_t)y.in * y.ld_n;
         B2_CHECK_CUDA(cudaMalloc(&y.w, nf * sizeof(float)));
         B2_CHECK_CUDA(cudaMalloc(&y.v, nf * sizeof(float)));
         B2_CHECK_CUDA(cudaMemset(y.v, 0, nf * sizeof(float)));
         B2_CHECK_CUDA(cudaMalloc(&y.wn, nf * sizeof(__nv_bfloat16)));
-        B2_CHECK_CUDA(cudaMalloc(&y.wt, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
         B2_CHECK_CUDA(cudaMemset(y.wn, 0, nf * sizeof(__nv_bfloat16)));
-        B2_CHECK_CUDA(cudaMemset(y.wt, 0, (size_t)y.out * y.ld_t * sizeof(__nv_bfloat16)));
         if (!net->fused_update) {
             B2_CHECK_CUDA(cudaMalloc(&y.g, nf * sizeof(float)));
             B2_CHECK_CUDA(cudaMemset(y.g, 0, nf * sizeof(float)));
         }
-        B2_TRY(make_tmap_bf16(&y.tm_wt, y.wt, y.in, y.out, y.ld_t, wide_b_box(net)));  // forward: N=out, K=in
-        B2_TRY(make_tmap_bf16(&y.tm_wn, y.wn, y.out, y.in, y.ld_n, wide_b_box(net)));  // delta:   N=in,  K=out
+        B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
     }
     return wide_upload_weights(net, w_host.data(), false);
 }
@@ -195,10 +160,8 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
 static void free_batch(b2nn_net *net) {
     WideBatch &b = net->wb;
     for (auto p : b.a) cudaFree(p);
-    for (auto p : b.at) cudaFree(p);
     for (auto p : b.d) cudaFree(p);
-    for (auto p : b.dt) cudaFree(p);
-    b.a.clear(); b.at.clear(); b.d.clear(); b.dt.clear();
+    b.a.clear(); b.d.clear();
     cudaFree(b.logits); cudaFree(b.row_loss); cudaFree(b.labels); cudaFree(b.tdense); cudaFree(b.xstage);
     cudaFree(b.loss_sum);
     b.logits = nullptr; b.row_loss = nullptr; b.labels = nullptr; b.tdense = nullptr; b.xstage = nullptr;
@@ -208,7 +171,7 @@ static void free_batch(b2nn_net *net) {
 
 void wide_free(b2nn_net *net) {
     free_batch(net);
-    for (auto &y : net->wide) { cudaFree(y.w); cudaFree(y.v); cudaFree(y.g); cudaFree(y.wn); cudaFree(y.wt); }
+    for (auto &y : net->wide) { cudaFree(y.w); cudaFree(y.v); cudaFree(y.g); cudaFree(y.wn); }
     net->wide.clear();
 }
 
@@ -218,24 +181,19 @@ int wide_ensure_batch(b2nn_net *net, int B) {
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     free_batch(net);
     const int nd = net->n_dims, L = nd - 1;
-    b.ldB = pad8(B);
-    b.a.assign(nd, nullptr); b.at.assign(nd, nullptr); b.d.assign(nd, nullptr); b.dt.assign(nd, nullptr);
-    b.tm_a.resize(nd); b.tm_at.resize(nd); b.tm_d.resize(nd); b.tm_dt.resize(nd);
+    b.a.assign(nd, nullptr); b.d.assign(nd, nullptr);
+    b.tm_a.resize(nd); b.tm_d.resize(nd);
     for (int l = 0; l < nd; l++) {
         const int dl = net->dims[l], ld = pad8(dl);
         if (l < L) {
             B2_CHECK_CUDA(cudaMalloc(&b.a[l], (size_t)B * ld * 2));
-            B2_CHECK_CUDA(cudaMalloc(&b.at[l], (size_t)dl * b.ldB * 2));
-            B2_CHECK_CUDA(cudaMemset(b.at[l], 0, (size_t)dl * b.ldB * 2));
-            B2_TRY(make_tmap_bf16(&b.tm_a[l], b.a[l], dl, B, ld, GEMM_BM));       // forward A: M=B, K=d_l
-            B2_TRY(make_tmap_bf16(&b.tm_at[l], b.at[l], B, dl, b.ldB, GEMM_BM));  // gradient A: M=d_l, K=B
+            B2_CHECK_CUDA(cudaMemset(b.a[l], 0, (size_t)B * ld * 2));
+            B2_TRY(make_tmap_bf16(&b.tm_a[l], b.a[l], dl, B, ld));
         }
         if (l >= 1) {
             B2_CHECK_CUDA(cudaMalloc(&b.d[l], (size_t)B * ld * 2));
-            B2_CHECK_CUDA(cudaMalloc(&b.dt[l], (size_t)dl * b.ldB * 2));
-            B2_CHECK_CUDA(cudaMemset(b.dt[l], 0, (size_t)dl * b.ldB * 2));
-            B2_TRY(make_tmap_bf16(&b.tm_d[l], b.d[l], dl, B, ld, GEMM_BM));       // delta A: M=B, K=d_l
-            B2_TRY(make_tmap_bf16(&b.tm_dt[l], b.dt[l], B, dl, b.ldB, wide_b_box(net)));  // gradient B: N=d_l, K=B
+            B2_CHECK_CUDA(cudaMemset(b.d[l], 0, (size_t)B * ld * 2));
+            B2_TRY(make_tmap_bf16(&b.tm_d[l], b.d[l], dl, B, ld));
         }
     }
     const int ldL = pad8(net->dims[L]);
@@ -249,25 +207,27 @@ int wide_ensure_batch(b2nn_net *net, int B) {
     return B2NN_OK;
 }
 
-// K8: a0 = f(X[idx]) as BF16 (+ transposed).  X device-visible in dtype x_dtype.
+// K8: a0 = f(X[idx]) as BF16.  X device-visible in dtype x_dtype.
 int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st) {
     WideBatch &b = net->wb;
     const int d0 = net->dims[0];
-    dim3 grid((d0 + 31) / 32, (B + 31) / 32), block(32, 8);
+    const long long total = (long long)B * ((d0 + 7) / 8);
+    long long blocks = (total + 255) / 256;
+    if (blocks > (long long)net->num_sms * 16) blocks = (long long)net->num_sms * 16;
+    const int grid = (int)blocks;
     const float p = (float)net->inner_param;
     switch (x_dtype) {
     case B2NN_DT_F64:
-        wide::input_prologue<double><<<grid, block, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p,
-                                                            b.a[0], pad8(d0), b.at[0], b.ldB);
+        wide::input_prologue<double><<<grid, 256, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
+                                                          pad8(d0));
         break;
     case B2NN_DT_F32:
-        wide::input_prologue<float><<<grid, block, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p,
-                                                           b.a[0], pad8(d0), b.at[0], b.ldB);
+        wide::input_prologue<float><<<grid, 256, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
+                                                         pad8(d0));
         break;
     case B2NN_DT_BF16:
-        wide::input_prologue<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
-                                                                   net->inner_act, p, b.a[0], pad8(d0), b.at[0],
-                                                                   b.ldB);
+        wide::input_prologue<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
+                                                                 net->inner_act, p, b.a[0], pad8(d0));
         break;
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
     }
@@ -276,7 +236,7 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     return B2NN_OK;
 }
 
-// forward GEMMs (replaces S:169-193); the last one keeps FP32 logits
+// forward GEMMs (replaces S:169-193): Z = A_l . W_l, A K-major, W MN-major; the last one keeps FP32 logits
 int wide_forward(b2nn_net *net, int B) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1;
@@ -287,11 +247,10 @@ int wide_forward(b2nn_net *net, int B) {
         g.act = net->inner_act; g.act_param = (float)net->inner_param;
         if (l + 1 < L) {
             g.out0 = b.a[l + 1]; g.ld0 = pad8(y.out);
-            g.out1 = b.at[l + 1]; g.ld1 = b.ldB;
-            B2_TRY(launch_gemm<EPI_ACT>(net, b.tm_a[l], y.tm_wt, g));
+            B2_TRY((launch_gemm<EPI_ACT, false, true>(net, b.tm_a[l], y.tm_w, g)));
         } else {
             g.out0 = b.logits; g.ld0 = pad8(y.out);
-            B2_TRY(launch_gemm<EPI_LOGITS>(net, b.tm_a[l], y.tm_wt, g));
+            B2_TRY((launch_gemm<EPI_LOGITS, false, true>(net, b.tm_a[l], y.tm_w, g)));
         }
     }
     return B2NN_OK;
@@ -301,17 +260,18 @@ int wide_forward(b2nn_net *net, int B) {
 int wide_output(b2nn_net *net, int B, bool dense_targets) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1, dL = net->dims[L], ldL = pad8(dL);
-    wide::output_delta<<<(B + 31) / 32, 256, 0, net->stream>>>(
+    wide::output_delta<<<(B + 7) / 8, 256, 0, net->stream>>>(
         b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
-        net->last_act, (float)net->last_param, b.d[L], ldL, b.dt[L], b.ldB, b.row_loss);
+        net->last_act, (float)net->last_param, b.d[L], ldL, b.row_loss);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
 }
 
-// backward: deltas (S:260-278), gradient GEMMs with the batch sum as the K dimension (S:279-283 +
-// S:305-322) and the momentum update (S:325-342) -- fused into the gradient GEMM's epilogue on one
-// GPU; all-reduced per layer on a side stream and then updated (K7) when data-parallel.
+// backward: deltas (S:260-278: D_l = D_l+1 . W_l^T, both operands K-major), gradient GEMMs with the batch sum
+// as the K dimension (S:279-283 + S:305-322: G_l = A_l^T . D_l+1, both operands MN-major) and the momentum
+// update (S:325-342) -- a streaming kernel after each gradient GEMM (or fused into its epilogue with
+// B2NN_FUSED_UPDATE=1); all-reduced per layer on a side stream first when data-parallel.
 int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1;
@@ -322,10 +282,9 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
             GemmArgs g{};
             g.M = B; g.N = y.in; g.K = y.out;
             g.out0 = b.d[l]; g.ld0 = pad8(y.in);
-            g.out1 = b.dt[l]; g.ld1 = b.ldB;
             g.aux = b.a[l]; g.ldaux = pad8(y.in);
             g.act = net->inner_act; g.act_param = (float)net->inner_param;
-            B2_TRY(launch_gemm<EPI_DX>(net, b.tm_d[l + 1], y.tm_wn, g));
+            B2_TRY((launch_gemm<EPI_DX, false, false>(net, b.tm_d[l + 1], y.tm_w, g)));
         }
         GemmArgs g{};
         g.M = y.in; g.N = y.out; g.K = B;
@@ -333,29 +292,19 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
         if (net->world == 1 && net->fused_update) {
             g.w = y.w; g.v = y.v;
             g.out0 = y.wn; g.ld0 = y.ld_n;
-            g.out1 = y.wt; g.ld1 = y.ld_t;
             g.scale = scale; g.momentum = (float)momentum;
-            B2_TRY(launch_gemm<EPI_DW_UPDATE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+            B2_TRY((launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
         } else if (net->world == 1) {
-            // gradient GEMM stores G (FP32), then the coalesced HBM-bound update kernel (K7)
             g.w = y.g;
-            B2_TRY(launch_gemm<EPI_DW_STORE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
-            dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
-            wide::sgd_update<<<grid, block, 0, net->stream>>>(y.g, y.w, y.v, y.in, y.out, y.ld_n, scale,
-                                                              (float)momentum, 0, y.wn, y.wt, y.ld_t);
-            net->launches++;
-            B2_CHECK_CUDA(cudaGetLastError());
+            B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
+            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, net->stream));
         } else {
             g.w = y.g;
-            B2_TRY(launch_gemm<EPI_DW_STORE>(net, b.tm_at[l], b.tm_dt[l + 1], g));
+            B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
             B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
             B2_CHECK_CUDA(cudaStreamWaitEvent(net->aux_stream, net->layer_events[l], 0));
             B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, net->aux_stream));
-            dim3 grid((y.out + 31) / 32, (y.in + 31) / 32), block(32, 8);
-            wide::sgd_update<<<grid, block, 0, net->aux_stream>>>(y.g, y.w, y.v, y.in, y.out, y.ld_n, scale,
-                                                                  (float)momentum, 0, y.wn, y.wt, y.ld_t);
-            net->launches++;
-            B2_CHECK_CUDA(cudaGetLastError());
+            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, net->aux_stream));
         }
     }
     if (net->world > 1) {

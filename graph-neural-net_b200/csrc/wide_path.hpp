@@ -4,8 +4,7 @@
 
 namespace b2nn {
 struct GemmArgs;
-int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t k, uint64_t rows, uint64_t ld, uint32_t box_rows);
-int wide_gemm_raw(b2nn_net *net, int epi, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g);
+int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld);
 int profile_flush(b2nn_net *net);
 int wide_init(b2nn_net *net, const std::vector<double> &w_host);
 void wide_free(b2nn_net *net);

@@ -28,7 +28,7 @@ def wide_net(g, dims, **kw):
 
 
 @pytest.mark.parametrize("M,K,N", [(128, 64, 256), (256, 512, 512), (100, 200, 1000), (4096, 1000, 136),
-                                    (37, 8, 8), (300, 4096, 264)])
+                                    (37, 8, 8), (300, 4096, 264), (2560, 128, 2048)])
 def test_gemm_forward_identity(g, M, K, N):
     """GeneralNeuralNet with identity activations makes propagate() the bare tcgen05 contraction
     y = x W: exercises TMA zero-fill on ragged M/N/K, the UMMA descriptors and the TMEM epilogue."""
