@@ -258,10 +258,15 @@ def run_b2nn(args):
                 "traffic": None}
 
     # ---- end to end: rows stay in pinned host memory, every step's batch crosses PCIe, per-step loss read back
-    x_host_bytes = B * dims[0] * x.dtype.itemsize
     if bf16:
-        ds_e2e = g.Dataset(net, x, labels=labels, location=g.capi.DATA_HOST_PINNED)
+        # host rows in the operand precision of this mode (BF16 bits, rounded to nearest even once at staging time,
+        # like the reference's one-off (byte & 0xff) / 255.0 at load, MNISTTrainer.java:97)
+        u = x.view(np.uint32)
+        x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+        x_host_bytes = B * dims[0] * x_host.dtype.itemsize
+        ds_e2e = g.Dataset(net, x_host, labels=labels, location=g.capi.DATA_HOST_PINNED)
     else:
+        x_host_bytes = 0
         ds_e2e = ds_dev
     train(ds_e2e, idx_warm[:min(3, idx_warm.shape[0])], want_loss=True)
     barrier()
@@ -273,8 +278,9 @@ def run_b2nn(args):
     e2e = {"value": world * B * K / e2e_s, "unit": "samples/s",
            "h2d_bytes_per_step": (x_host_bytes if bf16 else 0) + B * 4, "d2h_bytes_per_step": 8,
            "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]),
-           "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset: batch rows pulled over PCIe by the "
-                    "input prologue kernel every step" if bf16 else
+           "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset of BF16 rows: every step's batch rows are "
+                    "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
+                    "(double-buffered under the previous step's GEMMs); per-step loss read back" if bf16 else
                     "b2nn_train_indexed over the device-resident dataMaster (784-wide rows live on the GPU like "
                     "the reference's in-memory HashMap); index lists cross PCIe every call")}
     sampler_thread.active = False

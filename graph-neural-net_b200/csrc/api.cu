@@ -83,6 +83,8 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     {
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = fu != nullptr && fu[0] == '1';
+        const char *ou = getenv("B2NN_OVERLAP_UPDATE");
+        net->overlap_update = !(ou != nullptr && ou[0] == '0');
         const char *ff = getenv("B2NN_F64_FUSED");
         net->fused_f64_disabled = ff != nullptr && ff[0] == '0';
         net->coop_launch = prop.cooperativeLaunch != 0;

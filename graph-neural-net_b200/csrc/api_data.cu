@@ -1,7 +1,10 @@
 // api_data.cu -- C-ABI of libb2nn.so, part 3: the NeuralNetTrainer fast path -- datasets staged
 // once (dataMaster, T:35-40), many gradient steps per call driven by the caller's index lists
 // (T:88-90 + T:143-158), validate (T:102-113) and accuracy evaluation (M:159-197).
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.hpp"
 #include "f64_path.hpp"
@@ -44,12 +47,67 @@ int step_from_dataset(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx_dev, i
         return B2NN_OK;
     }
     B2_TRY(wide_prologue(net, ds->x_dev_alias, ds->x_dtype, idx_dev, B, net->stream));
-    if (ds->labels) B2_TRY(wide_gather_labels(net, ds->labels, idx_dev, B));
+    if (ds->labels) B2_TRY(wide_gather_labels(net, ds->labels, idx_dev, B, net->stream));
     else B2_TRY(wide_gather_targets(net, ds->t, idx_dev, B));
     B2_TRY(wide_forward(net, B));
-    B2_TRY(wide_output(net, B, ds->labels == nullptr));
+    B2_TRY(wide_output(net, B, ds->labels == nullptr, loss_slot_dev));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
-    if (loss_slot_dev) B2_TRY(wide_reduce(net, B, nullptr, nullptr, loss_slot_dev, nullptr));
+    return B2NN_OK;
+}
+
+// BF16 run of steps with the input double buffer: the prologue of step i+1 (for B2NN_DATA_HOST_PINNED rows
+// it IS the host->device copy, pulled over PCIe by a small grid) runs on the copy stream under step i's GEMMs.
+int wide_train_pipelined(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx_dev, int iters, int B, double step,
+                         double momentum, double *loss_dev) {
+    int bps = ds->location == B2NN_DATA_HOST_PINNED ? 1 : 16;
+    if (const char *e = getenv("B2NN_PROLOGUE_BPS")) bps = atoi(e) > 0 ? atoi(e) : bps;
+    cudaStream_t cs = net->copy_stream;
+    const bool trace = getenv("B2NN_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    if (trace) {
+        tev.resize(4 * (size_t)iters + 1);
+        for (auto &e : tev) B2_CHECK_CUDA(cudaEventCreate(&e));
+        B2_CHECK_CUDA(cudaEventRecord(tev[4 * (size_t)iters], net->stream));
+    }
+    auto prefetch = [&](int it) -> int {
+        const int q = it & 1;
+        wide_use_slot(net, q);
+        if (trace) B2_CHECK_CUDA(cudaEventRecord(tev[4 * it], cs));
+        B2_TRY(wide_prologue(net, ds->x_dev_alias, ds->x_dtype, idx_dev + (size_t)it * B, B, cs, bps));
+        B2_TRY(wide_gather_labels(net, ds->labels, idx_dev + (size_t)it * B, B, cs));
+        B2_CHECK_CUDA(cudaEventRecord(net->slot_ready[q], cs));
+        if (trace) B2_CHECK_CUDA(cudaEventRecord(tev[4 * it + 1], cs));
+        return B2NN_OK;
+    };
+    // the copy stream starts behind everything already queued on the main stream (index upload, earlier steps)
+    B2_CHECK_CUDA(cudaEventRecord(net->slot_free[0], net->stream));
+    B2_CHECK_CUDA(cudaStreamWaitEvent(cs, net->slot_free[0], 0));
+    B2_TRY(prefetch(0));
+    for (int it = 0; it < iters; it++) {
+        const int q = it & 1;
+        if (it + 1 < iters) {
+            if (it >= 1) B2_CHECK_CUDA(cudaStreamWaitEvent(cs, net->slot_free[q ^ 1], 0));  // step it-1 is done with it
+            B2_TRY(prefetch(it + 1));
+        }
+        wide_use_slot(net, q);
+        B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->slot_ready[q], 0));
+        if (trace) B2_CHECK_CUDA(cudaEventRecord(tev[4 * it + 2], net->stream));
+        B2_TRY(wide_forward(net, B));
+        B2_TRY(wide_output(net, B, false, loss_dev ? loss_dev + it : nullptr));
+        B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
+        B2_CHECK_CUDA(cudaEventRecord(net->slot_free[q], net->stream));
+        if (trace) B2_CHECK_CUDA(cudaEventRecord(tev[4 * it + 3], net->stream));
+    }
+    if (trace) {  // measurement aid: per-step timeline (ms since the call) of the two streams
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(cs));
+        for (int it = 0; it < iters && it < 12; it++) {
+            float t[4];
+            for (int k = 0; k < 4; k++) cudaEventElapsedTime(&t[k], tev[4 * (size_t)iters], tev[4 * it + k]);
+            fprintf(stderr, "[b2nn trace] step %d prologue %.3f-%.3f compute %.3f-%.3f\n", it, t[0], t[1], t[2], t[3]);
+        }
+        for (auto &e : tev) cudaEventDestroy(e);
+    }
     return B2NN_OK;
 }
 
@@ -198,9 +256,14 @@ int b2nn_train_indexed(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx, int3
         B2_TRY(f64_fused_train(net, (const double *)ds->x_dev_alias, ds->xu8, ds->t, ds->labels, idx_dev, iters, B, step,
                                momentum, loss_dev));
     } else {
-        for (int it = 0; it < iters; it++)
-            B2_TRY(step_from_dataset(net, ds, idx_dev + (size_t)it * B, B, step, momentum,
-                                     loss_dev ? loss_dev + it : nullptr));
+        const char *pl = getenv("B2NN_PIPELINE");
+        if (net->precision == B2NN_PREC_BF16 && ds->labels != nullptr && iters > 1 && !(pl && pl[0] == '0')) {
+            B2_TRY(wide_train_pipelined(net, ds, idx_dev, iters, B, step, momentum, loss_dev));
+        } else {
+            for (int it = 0; it < iters; it++)
+                B2_TRY(step_from_dataset(net, ds, idx_dev + (size_t)it * B, B, step, momentum,
+                                         loss_dev ? loss_dev + it : nullptr));
+        }
     }
     if (per_step_loss_or_null) {
         B2_CHECK_CUDA(cudaMemcpyAsync(per_step_loss_or_null, loss_dev, loss_bytes, cudaMemcpyDeviceToHost, net->stream));

@@ -217,11 +217,10 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
                                   net->stream));
     B2_TRY(wide_gather_targets(net, (const double *)net->dscratch, nullptr, B));
     B2_TRY(wide_forward(net, B));
-    B2_TRY(wide_output(net, B, true));
+    if (mean_loss_or_null) B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
+    B2_TRY(wide_output(net, B, true, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
     if (mean_loss_or_null) {
-        B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
-        B2_TRY(wide_reduce(net, B, nullptr, nullptr, net->wb.loss_sum, nullptr));
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
@@ -242,11 +241,10 @@ int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, co
     B2_CHECK_CUDA(cudaMemcpyAsync(net->wb.labels, labels, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice,
                                   net->stream));
     B2_TRY(wide_forward(net, B));
-    B2_TRY(wide_output(net, B, false));
+    if (mean_loss_or_null) B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
+    B2_TRY(wide_output(net, B, false, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
     if (mean_loss_or_null) {
-        B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
-        B2_TRY(wide_reduce(net, B, nullptr, nullptr, net->wb.loss_sum, nullptr));
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));

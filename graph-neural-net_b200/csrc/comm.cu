@@ -90,18 +90,14 @@ int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
     net->nccl_comm = c;
     net->rank = rank;
     net->world = world;
-    B2_CHECK_CUDA(cudaStreamCreateWithFlags(&net->aux_stream, cudaStreamNonBlocking));
     const int L = net->n_dims - 1;
-    net->layer_events.resize(L);
     for (int l = 0; l < L; l++) {
-        B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->layer_events[l], cudaEventDisableTiming));
         auto &y = net->wide[l];
         if (y.g == nullptr) {
             B2_CHECK_CUDA(cudaMalloc(&y.g, (size_t)y.in * y.ld_n * sizeof(float)));
             B2_CHECK_CUDA(cudaMemset(y.g, 0, (size_t)y.in * y.ld_n * sizeof(float)));
         }
     }
-    B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->comm_done, cudaEventDisableTiming));
     return B2NN_OK;
 }
 
@@ -111,10 +107,6 @@ void comm_destroy(b2nn_net *net) {
         if (a) a->CommDestroy((NcclComm)net->nccl_comm);
         net->nccl_comm = nullptr;
     }
-    for (auto e : net->layer_events) cudaEventDestroy(e);
-    net->layer_events.clear();
-    if (net->comm_done) { cudaEventDestroy(net->comm_done); net->comm_done = nullptr; }
-    if (net->aux_stream) { cudaStreamDestroy(net->aux_stream); net->aux_stream = nullptr; }
 }
 
 int comm_allreduce_sum_f32(b2nn_net *net, float *buf, size_t count, cudaStream_t st) {

@@ -89,6 +89,13 @@ struct WideBatch {
     void *xstage = nullptr;            // staged raw input rows [B][d0] (any dtype, 8 B / element max)
     std::vector<CUtensorMap> tm_a, tm_d;  // 64 x 64 box maps over a[l], d[l]
     double *loss_sum = nullptr;        // device scalar(s)
+    double *block_partial = nullptr;   // per-block loss partials of the output kernel
+    unsigned int *block_counter = nullptr;
+    // input double buffer: while step i computes from slot i&1, the prologue of step i+1 fills the other
+    // slot on the copy stream.  a[0] / tm_a[0] / labels above alias the slot in use.
+    __nv_bfloat16 *a0_slot[2] = {nullptr, nullptr};
+    int32_t *labels_slot[2] = {nullptr, nullptr};
+    CUtensorMap tm_a0_slot[2];
 };
 
 }  // namespace b2nn
@@ -117,7 +124,9 @@ struct b2nn_net {
     std::vector<int64_t> w_off;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    cudaStream_t aux_stream = nullptr;  // copies / collectives
+    cudaStream_t aux_stream = nullptr;  // updates / collectives
+    cudaStream_t copy_stream = nullptr;  // input prologue of the next step
+    cudaEvent_t slot_ready[2] = {nullptr, nullptr}, slot_free[2] = {nullptr, nullptr};
     int num_sms = 0;
     int64_t launches = 0;
 
@@ -144,7 +153,8 @@ struct b2nn_net {
     int max_smem_optin = 0;
 
     // BF16 path
-    bool fused_update = false;  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
+    bool fused_update = false;
+    bool overlap_update = true;  // layer l's update on the side stream under layer l-1's GEMMs (B2NN_OVERLAP_UPDATE=0: off)  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
     b2nn::WideBatch wb;
 

@@ -72,10 +72,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 __global__ void __launch_bounds__(256)
 output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ labels,
              const float *__restrict__ tdense, int ld_t, int B, int dL, int kind, int last_act, float last_param,
-             __nv_bfloat16 *__restrict__ d, int ld_d, float *__restrict__ row_loss) {
-    const int lane = threadIdx.x & 31;
-    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (b >= B) return;
+             __nv_bfloat16 *__restrict__ d, int ld_d, float *__restrict__ row_loss, double *loss_slot,
+             double *__restrict__ block_partial, unsigned int *block_counter) {
+    __shared__ float s_row[8];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x * (blockDim.x >> 5) + warp;
+    float lacc = 0.f;
+    if (b < B) {
     const float *z = Z + (size_t)b * ld_z;
     const float *t = tdense ? tdense + (size_t)b * ld_t : nullptr;
     const int lab = labels ? labels[b] : -1;
@@ -91,7 +95,6 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
         inv = 1.f / sum;
         lse = __logf(sum);
     }
-    float lacc = 0.f;
     // two columns per lane per step -> 4-byte stores, 128 B per warp
     for (int c0 = 2 * lane; c0 < dL; c0 += 64) {
         float dv[2] = {0.f, 0.f};
@@ -118,6 +121,28 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
     }
     lacc = warp_sum(lacc);
     if (lane == 0 && row_loss) row_loss[b] = lacc;
+    }
+    // optional batch loss sum with a fixed summation order (rows within a block, then blocks in index order by
+    // whichever block finishes last), so a run is reproducible bit for bit and needs no extra launch
+    if (loss_slot == nullptr) return;
+    if (lane == 0) s_row[warp] = lacc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += (double)s_row[w];
+        block_partial[blockIdx.x] = s;
+        __threadfence();
+        s_last = atomicAdd(block_counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && warp == 0) {
+        __threadfence();
+        double s = 0.0;
+        for (int i = lane; i < (int)gridDim.x; i += 32) s += __ldcg(block_partial + i);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) { *loss_slot += s; *block_counter = 0u; }
+    }
 }
 
 // Evaluation row pass: one warp per row.  `>=` argmax so the LAST maximal index wins

@@ -135,8 +135,32 @@ int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity) {
     return B2NN_OK;
 }
 
+// The L1/shared-memory split of an SM can only change while the SM is empty, and the GEMM CTAs need ~198 KB of
+// shared memory: a resident block of a kernel that asked for the default (L1-heavy) split keeps GEMM CTAs off
+// that SM until it exits.  Every kernel that runs beside or between the GEMMs therefore asks for the
+// max-shared carve-out too, so the side-stream update / input prologue really overlap and no
+// reconfiguration drain happens at kernel boundaries.
+static int prefer_max_shared_carveout() {
+    static bool done = false;
+    if (done) return B2NN_OK;
+    const int c = cudaSharedmemCarveoutMaxShared;
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::sgd_update, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<double>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<float>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<__nv_bfloat16>,
+                                       cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::output_delta, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::reduce_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_labels, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_targets, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::eval_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    done = true;
+    return B2NN_OK;
+}
+
 int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
     const int L = net->n_dims - 1;
+    B2_TRY(prefer_max_shared_carveout());
     net->wide.resize(L);
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
@@ -154,25 +178,61 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         }
         B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
     }
+    // side stream: the HBM-bound update (and, data-parallel, the all-reduce before it) of layer l runs there
+    // while the tensor cores go on with layer l-1's contractions
+    B2_CHECK_CUDA(cudaStreamCreateWithFlags(&net->aux_stream, cudaStreamNonBlocking));
+    net->layer_events.resize(L);
+    for (int l = 0; l < L; l++)
+        B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->layer_events[l], cudaEventDisableTiming));
+    B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->comm_done, cudaEventDisableTiming));
+    B2_CHECK_CUDA(cudaStreamCreateWithFlags(&net->copy_stream, cudaStreamNonBlocking));
+    for (int q = 0; q < 2; q++) {
+        B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->slot_ready[q], cudaEventDisableTiming));
+        B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->slot_free[q], cudaEventDisableTiming));
+    }
     return wide_upload_weights(net, w_host.data(), false);
 }
 
 static void free_batch(b2nn_net *net) {
     WideBatch &b = net->wb;
+    if (!b.a.empty()) b.a[0] = nullptr;  // alias of a slot
+    b.labels = nullptr;
+    for (int q = 0; q < 2; q++) {
+        cudaFree(b.a0_slot[q]); cudaFree(b.labels_slot[q]);
+        b.a0_slot[q] = nullptr; b.labels_slot[q] = nullptr;
+    }
     for (auto p : b.a) cudaFree(p);
     for (auto p : b.d) cudaFree(p);
     b.a.clear(); b.d.clear();
-    cudaFree(b.logits); cudaFree(b.row_loss); cudaFree(b.labels); cudaFree(b.tdense); cudaFree(b.xstage);
-    cudaFree(b.loss_sum);
-    b.logits = nullptr; b.row_loss = nullptr; b.labels = nullptr; b.tdense = nullptr; b.xstage = nullptr;
+    cudaFree(b.logits); cudaFree(b.row_loss); cudaFree(b.tdense); cudaFree(b.xstage);
+    cudaFree(b.loss_sum); cudaFree(b.block_partial); cudaFree(b.block_counter);
+    b.block_partial = nullptr; b.block_counter = nullptr;
+    b.logits = nullptr; b.row_loss = nullptr; b.tdense = nullptr; b.xstage = nullptr;
     b.loss_sum = nullptr;
     b.B = 0;
 }
 
 void wide_free(b2nn_net *net) {
     free_batch(net);
+    for (auto e : net->layer_events) cudaEventDestroy(e);
+    net->layer_events.clear();
+    if (net->comm_done) { cudaEventDestroy(net->comm_done); net->comm_done = nullptr; }
+    if (net->aux_stream) { cudaStreamDestroy(net->aux_stream); net->aux_stream = nullptr; }
+    if (net->copy_stream) { cudaStreamDestroy(net->copy_stream); net->copy_stream = nullptr; }
+    for (int q = 0; q < 2; q++) {
+        if (net->slot_ready[q]) { cudaEventDestroy(net->slot_ready[q]); net->slot_ready[q] = nullptr; }
+        if (net->slot_free[q]) { cudaEventDestroy(net->slot_free[q]); net->slot_free[q] = nullptr; }
+    }
     for (auto &y : net->wide) { cudaFree(y.w); cudaFree(y.v); cudaFree(y.g); cudaFree(y.wn); }
     net->wide.clear();
+}
+
+// point a[0] / tm_a[0] / labels at input slot q
+void wide_use_slot(b2nn_net *net, int q) {
+    WideBatch &b = net->wb;
+    b.a[0] = b.a0_slot[q];
+    b.tm_a[0] = b.tm_a0_slot[q];
+    b.labels = b.labels_slot[q];
 }
 
 int wide_ensure_batch(b2nn_net *net, int B) {
@@ -185,7 +245,14 @@ int wide_ensure_batch(b2nn_net *net, int B) {
     b.tm_a.resize(nd); b.tm_d.resize(nd);
     for (int l = 0; l < nd; l++) {
         const int dl = net->dims[l], ld = pad8(dl);
-        if (l < L) {
+        if (l == 0) {
+            for (int q = 0; q < 2; q++) {
+                B2_CHECK_CUDA(cudaMalloc(&b.a0_slot[q], (size_t)B * ld * 2));
+                B2_CHECK_CUDA(cudaMemset(b.a0_slot[q], 0, (size_t)B * ld * 2));
+                B2_TRY(make_tmap_bf16(&b.tm_a0_slot[q], b.a0_slot[q], dl, B, ld));
+                B2_CHECK_CUDA(cudaMalloc(&b.labels_slot[q], (size_t)B * sizeof(int32_t)));
+            }
+        } else if (l < L) {
             B2_CHECK_CUDA(cudaMalloc(&b.a[l], (size_t)B * ld * 2));
             B2_CHECK_CUDA(cudaMemset(b.a[l], 0, (size_t)B * ld * 2));
             B2_TRY(make_tmap_bf16(&b.tm_a[l], b.a[l], dl, B, ld));
@@ -199,34 +266,47 @@ int wide_ensure_batch(b2nn_net *net, int B) {
     const int ldL = pad8(net->dims[L]);
     B2_CHECK_CUDA(cudaMalloc(&b.logits, (size_t)B * ldL * sizeof(float)));
     B2_CHECK_CUDA(cudaMalloc(&b.row_loss, (size_t)B * sizeof(float)));
-    B2_CHECK_CUDA(cudaMalloc(&b.labels, (size_t)B * sizeof(int32_t)));
     B2_CHECK_CUDA(cudaMalloc(&b.tdense, (size_t)B * ldL * sizeof(float)));
     B2_CHECK_CUDA(cudaMalloc(&b.xstage, (size_t)B * net->dims[0] * sizeof(double)));
     B2_CHECK_CUDA(cudaMalloc(&b.loss_sum, 2 * sizeof(double)));
+    B2_CHECK_CUDA(cudaMalloc(&b.block_partial, (size_t)((B + 7) / 8) * sizeof(double)));
+    B2_CHECK_CUDA(cudaMalloc(&b.block_counter, sizeof(unsigned int)));
+    B2_CHECK_CUDA(cudaMemset(b.block_counter, 0, sizeof(unsigned int)));
     b.B = B;
+    wide_use_slot(net, 0);
     return B2NN_OK;
 }
 
 // K8: a0 = f(X[idx]) as BF16.  X device-visible in dtype x_dtype.
-int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st) {
+int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st,
+                  int blocks_per_sm) {
     WideBatch &b = net->wb;
     const int d0 = net->dims[0];
     const long long total = (long long)B * ((d0 + 7) / 8);
     long long blocks = (total + 255) / 256;
-    if (blocks > (long long)net->num_sms * 16) blocks = (long long)net->num_sms * 16;
-    const int grid = (int)blocks;
+    if (blocks > (long long)net->num_sms * blocks_per_sm) blocks = (long long)net->num_sms * blocks_per_sm;
+    int grid = (int)blocks;
+    int thr = 256;
+    if (blocks_per_sm == 1) {
+        // rows in mapped pinned host memory: one 64-thread block per SM keeps PCIe saturated (~50 GB/s) while
+        // bounding the number of multi-microsecond reads in flight; with more, the concurrently running GEMMs
+        // slowed down 2.8x (measured, profiles/r01_notes.md)
+        thr = 64;
+        grid = net->num_sms;
+    }
+    if (const char *e = getenv("B2NN_PROLOGUE_THREADS")) { thr = atoi(e); grid = net->num_sms * blocks_per_sm; }
     const float p = (float)net->inner_param;
     switch (x_dtype) {
     case B2NN_DT_F64:
-        wide::input_prologue<double><<<grid, 256, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
+        wide::input_prologue<double><<<grid, thr, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
                                                           pad8(d0));
         break;
     case B2NN_DT_F32:
-        wide::input_prologue<float><<<grid, 256, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
+        wide::input_prologue<float><<<grid, thr, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
                                                          pad8(d0));
         break;
     case B2NN_DT_BF16:
-        wide::input_prologue<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
+        wide::input_prologue<__nv_bfloat16><<<grid, thr, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
                                                                  net->inner_act, p, b.a[0], pad8(d0));
         break;
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
@@ -257,12 +337,12 @@ int wide_forward(b2nn_net *net, int B) {
 }
 
 // K5/K6: output delta + per-row loss
-int wide_output(b2nn_net *net, int B, bool dense_targets) {
+int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1, dL = net->dims[L], ldL = pad8(dL);
     wide::output_delta<<<(B + 7) / 8, 256, 0, net->stream>>>(
         b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
-        net->last_act, (float)net->last_param, b.d[L], ldL, b.row_loss);
+        net->last_act, (float)net->last_param, b.d[L], ldL, b.row_loss, loss_slot_dev, b.block_partial, b.block_counter);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -276,6 +356,7 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1;
     const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
+    bool side = false;
     for (int l = L - 1; l >= 0; l--) {
         WideLayer &y = net->wide[l];
         if (l >= 1) {
@@ -294,20 +375,21 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
             g.out0 = y.wn; g.ld0 = y.ld_n;
             g.scale = scale; g.momentum = (float)momentum;
             B2_TRY((launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
-        } else if (net->world == 1) {
-            g.w = y.g;
-            B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
-            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, net->stream));
         } else {
             g.w = y.g;
             B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
-            B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
-            B2_CHECK_CUDA(cudaStreamWaitEvent(net->aux_stream, net->layer_events[l], 0));
-            B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, net->aux_stream));
-            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, net->aux_stream));
+            // layer 0 has nothing left to overlap with on one GPU: update it in stream order
+            cudaStream_t us = (net->world > 1 || (l > 0 && net->overlap_update)) ? net->aux_stream : net->stream;
+            if (us != net->stream) {
+                B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
+                B2_CHECK_CUDA(cudaStreamWaitEvent(us, net->layer_events[l], 0));
+                side = true;
+            }
+            if (net->world > 1) B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, us));
+            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, us));
         }
     }
-    if (net->world > 1) {
+    if (side) {
         B2_CHECK_CUDA(cudaEventRecord(net->comm_done, net->aux_stream));
         B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->comm_done, 0));
     }
@@ -334,8 +416,8 @@ int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t 
     return B2NN_OK;
 }
 
-int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B) {
-    wide::gather_labels<<<(B + 255) / 256, 256, 0, net->stream>>>(labels, idx_dev, B, net->wb.labels);
+int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B, cudaStream_t st) {
+    wide::gather_labels<<<(B + 255) / 256, 256, 0, st>>>(labels, idx_dev, B, net->wb.labels);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;

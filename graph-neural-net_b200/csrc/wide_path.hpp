@@ -11,13 +11,15 @@ void wide_free(b2nn_net *net);
 int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity);
 int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity);
 int wide_ensure_batch(b2nn_net *net, int B);
-int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st);
+void wide_use_slot(b2nn_net *net, int q);
+int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_dev, int B, cudaStream_t st,
+                  int blocks_per_sm = 16);
 int wide_forward(b2nn_net *net, int B);
-int wide_output(b2nn_net *net, int B, bool dense_targets);
+int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev = nullptr);
 int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum);
 int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss);
 int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,
                 long long *hits_dev);
-int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B);
+int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B, cudaStream_t st);
 int wide_gather_targets(b2nn_net *net, const double *T, const int32_t *idx_dev, int B);
 }  // namespace b2nn
