@@ -83,6 +83,13 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     {
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = fu != nullptr && fu[0] == '1';
+        net->trace = getenv("B2NN_TRACE") != nullptr;
+        if (const char *dc = getenv("B2NN_DP_CTAS")) { if (atoi(dc) > 0) net->dp_ctas = atoi(dc); }
+        const char *dt = getenv("B2NN_DYNAMIC_TILES");
+        net->dynamic_tiles = dt != nullptr && dt[0] == '1';
+        net->dynamic_tiles_forced = dt != nullptr;
+        const char *br = getenv("B2NN_BACKWARD_REORDER");
+        net->backward_reorder = !(br != nullptr && br[0] == '0');
         const char *ou = getenv("B2NN_OVERLAP_UPDATE");
         net->overlap_update = !(ou != nullptr && ou[0] == '0');
         const char *ff = getenv("B2NN_F64_FUSED");
@@ -232,6 +239,18 @@ int b2nn_comm_init(b2nn_net *net, const void *id128, int32_t rank, int32_t world
     B2_REQUIRE(net != nullptr && id128 != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
     B2_CHECK_CUDA(cudaSetDevice(net->device));
     return comm_init(net, id128, rank, world);
+}
+
+int b2nn_comm_ipc_export(b2nn_net *net, void *handle64) {
+    B2_REQUIRE(net != nullptr && handle64 != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    return comm_ipc_export(net, handle64);
+}
+
+int b2nn_comm_ipc_import(b2nn_net *net, const void *handles, int32_t world) {
+    B2_REQUIRE(net != nullptr && handles != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    return comm_ipc_import(net, handles, world);
 }
 
 }  // extern "C"

@@ -91,6 +91,7 @@ int wide_train_pipelined(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx_dev
         }
         wide_use_slot(net, q);
         B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->slot_ready[q], 0));
+        trace_mark(net, net->stream, "step", it);
         if (trace) B2_CHECK_CUDA(cudaEventRecord(tev[4 * it + 2], net->stream));
         B2_TRY(wide_forward(net, B));
         B2_TRY(wide_output(net, B, false, loss_dev ? loss_dev + it : nullptr));
@@ -265,6 +266,8 @@ int b2nn_train_indexed(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx, int3
                                          loss_dev ? loss_dev + it : nullptr));
         }
     }
+    if (net->precision == B2NN_PREC_BF16) B2_TRY(wide_join(net));  // side-stream updates belong to this call
+    if (net->trace) trace_dump(net, 3, 2);
     if (per_step_loss_or_null) {
         B2_CHECK_CUDA(cudaMemcpyAsync(per_step_loss_or_null, loss_dev, loss_bytes, cudaMemcpyDeviceToHost, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));

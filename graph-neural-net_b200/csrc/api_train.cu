@@ -220,6 +220,7 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
     if (mean_loss_or_null) B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
     B2_TRY(wide_output(net, B, true, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
+    B2_TRY(wide_join(net));
     if (mean_loss_or_null) {
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {
@@ -244,6 +245,7 @@ int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, co
     if (mean_loss_or_null) B2_CHECK_CUDA(cudaMemsetAsync(net->wb.loss_sum, 0, sizeof(double), net->stream));
     B2_TRY(wide_output(net, B, false, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
+    B2_TRY(wide_join(net));
     if (mean_loss_or_null) {
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {

@@ -5,6 +5,8 @@
 
 #include <dlfcn.h>
 
+#include <cstring>
+
 namespace b2nn {
 
 namespace {
@@ -101,7 +103,44 @@ int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
     return B2NN_OK;
 }
 
+// ---- peer memory (CUDA IPC): lets the fused reduce/update kernel (dp_kernels.cuh) address every rank's arena ----
+int comm_ipc_export(b2nn_net *net, void *handle64) {
+    B2_REQUIRE(net->arena != nullptr, B2NN_ERR_UNSUPPORTED, "peer memory is for BF16 nets");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    B2_CHECK_CUDA(cudaIpcGetMemHandle(&h, net->arena));
+    memcpy(handle64, &h, 64);
+    return B2NN_OK;
+}
+
+int comm_ipc_import(b2nn_net *net, const void *handles, int world) {
+    B2_REQUIRE(world == net->world && world <= DP_MAX_WORLD, B2NN_ERR_INVALID_ARG,
+               "world %d does not match the communicator (%d) or exceeds %d", world, net->world, DP_MAX_WORLD);
+    B2_REQUIRE(net->n_dims - 1 <= 32, B2NN_ERR_UNSUPPORTED, "peer-memory path supports up to 32 weight matrices");
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    net->peer_arena.assign(world, nullptr);
+    for (int p = 0; p < world; p++) {
+        if (p == net->rank) { net->peer_arena[p] = net->arena; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char *)handles + 64 * (size_t)p, 64);
+        void *ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            set_error("cudaIpcOpenMemHandle(rank %d) -> %s", p, cudaGetErrorString(e));
+            for (int q = 0; q < p; q++)
+                if (q != net->rank && net->peer_arena[q]) cudaIpcCloseMemHandle(net->peer_arena[q]);
+            net->peer_arena.clear();
+            return B2NN_ERR_CUDA;
+        }
+        net->peer_arena[p] = (char *)ptr;
+    }
+    return B2NN_OK;
+}
+
 void comm_destroy(b2nn_net *net) {
+    for (size_t p = 0; p < net->peer_arena.size(); p++)
+        if ((int)p != net->rank && net->peer_arena[p]) cudaIpcCloseMemHandle(net->peer_arena[p]);
+    net->peer_arena.clear();
     if (net->nccl_comm) {
         NcclApi *a = nccl();
         if (a) a->CommDestroy((NcclComm)net->nccl_comm);

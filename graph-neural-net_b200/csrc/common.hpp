@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/b2nn.h"
@@ -59,6 +60,8 @@ struct JavaRandom {
 };
 
 inline int pad8(int x) { return (x + 7) & ~7; }
+constexpr size_t DP_FLAG_BYTES = 8192;  // head of the arena: cross-GPU flags of the fused reduce/update kernel
+constexpr int DP_MAX_WORLD = 8;
 
 
 // ---- per-layer state ----------------------------------------------------------------------
@@ -153,16 +156,31 @@ struct b2nn_net {
     int max_smem_optin = 0;
 
     // BF16 path
+    unsigned int *tile_counter = nullptr;  // dynamic tile scheduler of the GEMM kernel (all launches are stream-ordered)
+    bool dynamic_tiles_forced = false;
+    bool dynamic_tiles = false;  // B2NN_DYNAMIC_TILES=1, or data-parallel (NCCL kernels share the SMs)
+    bool backward_reorder = true;  // all deltas first, then gradients bottom-up (B2NN_BACKWARD_REORDER=0: layer by layer)
     bool fused_update = false;
     bool overlap_update = true;  // layer l's update on the side stream under layer l-1's GEMMs (B2NN_OVERLAP_UPDATE=0: off)  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
     b2nn::WideBatch wb;
 
     // data-parallel
+    char *arena = nullptr;           // flags + all layers' g / w / v / wn (one allocation, one IPC handle)
+    size_t arena_bytes = 0;
+    std::vector<char *> peer_arena;  // [world] peers' arenas mapped with CUDA IPC (own entry = arena); empty: NCCL path
+    int dp_ctas = 148;                // CTAs of the fused reduce/update kernel (B2NN_DP_CTAS)
+    unsigned int dp_seq = 0;         // sequence number of the cross-GPU flag handshakes
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;
     std::vector<cudaEvent_t> layer_events;
+    std::vector<cudaEvent_t> upd_done;   // per layer: side-stream update finished
+    std::vector<char> upd_pending;       // per layer: upd_done[l] not yet waited for by the main stream
     cudaEvent_t comm_done = nullptr;
+
+    // B2NN_TRACE=1: timeline marks (timing events) on the main / side streams, dumped by b2nn_train_indexed
+    bool trace = false;
+    std::vector<std::pair<cudaEvent_t, std::string>> trace_marks;
 
     // profiling (b2nn_profile_enable): event pairs around GEMM launches
     bool profiling = false;

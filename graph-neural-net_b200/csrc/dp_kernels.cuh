@@ -1,0 +1,152 @@
+// dp_kernels.cuh -- data-parallel gradient exchange fused with the optimizer step, over NVLink peer memory.
+//
+// The serial reference sums per-sample gradients over the batch and applies one momentum update
+// (src/SoftmaxCrossEntropyNeuralNet.java:305-342).  With the batch split over G GPUs the sum becomes a sum
+// over GPUs.  Instead of all-reduce (2(G-1)/G x 4 B per parameter on the wire) + a separate update kernel,
+// ONE kernel per layer does reduce-scatter + update + all-gather with plain loads / stores on the peers'
+// memory (every GPU of an NVSwitch box reaches every peer at full NVLink bandwidth):
+//   rank r owns the r-th slice of the layer's parameters (optimizer state is sharded: master w and v of a
+//   slice live only on its owner);
+//   1. handshake: tell every peer "my gradient of layer l is complete", wait for theirs;
+//   2. for each owned float4: g = sum over ranks 0..G-1 (fixed order) of the peers' gradient, read over
+//      NVLink; v = scale*g + mu*v; w -= v; the BF16 operand copy of w is stored into EVERY rank's wn;
+//   3. handshake: "my slice is written everywhere"; the kernel ends when all peers said so, i.e. when this
+//      rank's wn is complete and its gradient buffer is no longer being read.
+// Wire traffic per parameter: (G-1)/G x (4 B in + 2 B out); the gradient never makes a second trip through HBM.
+#pragma once
+#include <cuda_bf16.h>
+
+#include <cstdint>
+
+#include "common.hpp"
+#include "gemm_tcgen05.cuh"
+
+namespace b2nn {
+namespace dp {
+
+constexpr int MAX_LAYERS = 32;
+constexpr int DP_THREADS = 256;
+// layout of the flag block at the head of every arena (DP_FLAG_BYTES)
+struct Flags {
+    unsigned int ready[MAX_LAYERS][DP_MAX_WORLD];  // [l][p]: rank p's gradient of layer l is complete (sequence number)
+    unsigned int done[MAX_LAYERS][DP_MAX_WORLD];   // [l][p]: rank p has written its slice of layer l everywhere
+    unsigned int go[MAX_LAYERS];                   // local: CTA 0 saw every peer's ready flag
+    unsigned int finished[MAX_LAYERS];             // local: CTAs of this launch that finished their part
+};
+static_assert(sizeof(Flags) <= DP_FLAG_BYTES, "flag block does not fit");
+
+struct Args {
+    char *arena[DP_MAX_WORLD];  // every rank's arena (own entry included), same layout everywhere
+    int world, rank, layer;
+    unsigned long long off_g, off_w, off_v, off_wn;  // byte offsets of this layer's arrays inside an arena
+    long long n4;               // float4 elements of the layer (padded [in][ld_n] array)
+    float scale, momentum;
+    unsigned int seq;           // handshake sequence number, identical on all ranks for this launch
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(DP_THREADS)
+reduce_update_kernel(const Args a) {
+    Flags *mine = reinterpret_cast<Flags *>(a.arena[a.rank]);
+    const int l = a.layer;
+    // ---- 1. every rank's gradient is complete ----
+    if (blockIdx.x == 0) {
+        if ((int)threadIdx.x < a.world) {
+            Flags *peer = reinterpret_cast<Flags *>(a.arena[threadIdx.x]);
+            __threadfence_system();
+            st_release_sys(&peer->ready[l][a.rank], a.seq);
+            while (ld_acquire_sys(&mine->ready[l][threadIdx.x]) != a.seq) {
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&mine->go[l]), "r"(a.seq) : "memory");
+        }
+    } else {
+        if (threadIdx.x == 0)
+            while (ld_acquire_gpu(&mine->go[l]) != a.seq) {
+            }
+        __syncthreads();
+    }
+
+    // ---- 2. owned slice: reduce over the peers, update, broadcast the BF16 copy ----
+    const long long lo = (long long)a.rank * a.n4 / a.world, hi = (long long)(a.rank + 1) * a.n4 / a.world;
+    float4 *w = reinterpret_cast<float4 *>(a.arena[a.rank] + a.off_w);
+    float4 *v = reinterpret_cast<float4 *>(a.arena[a.rank] + a.off_v);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    // NVLink reads are latency-bound per request: keep UNROLL x world 16-byte loads in flight per thread
+    constexpr int UNROLL = 8;
+    for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += stride * UNROLL) {
+        float4 g[UNROLL], wv[UNROLL], vv[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < DP_MAX_WORLD; p++) {
+            if (p < a.world) {
+                const float4 *gp = reinterpret_cast<const float4 *>(a.arena[p] + a.off_g);
+                float4 t[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; u++) {
+                    const long long q = q0 + u * stride;
+                    t[u] = q < hi ? __ldcg(gp + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < UNROLL; u++) { g[u].x += t[u].x; g[u].y += t[u].y; g[u].z += t[u].z; g[u].w += t[u].w; }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            const long long q = q0 + u * stride;
+            if (q < hi) { wv[u] = w[q]; vv[u] = v[q]; }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            const long long q = q0 + u * stride;
+            if (q >= hi) continue;
+            float4 &W = wv[u], &V = vv[u];
+            V.x = a.scale * g[u].x + a.momentum * V.x; V.y = a.scale * g[u].y + a.momentum * V.y;
+            V.z = a.scale * g[u].z + a.momentum * V.z; V.w = a.scale * g[u].w + a.momentum * V.w;
+            W.x -= V.x; W.y -= V.y; W.z -= V.z; W.w -= V.w;
+            v[q] = V;
+            w[q] = W;
+            const uint2 b = make_uint2(pack_bf16x2(W.x, W.y), pack_bf16x2(W.z, W.w));
+#pragma unroll
+            for (int p = 0; p < DP_MAX_WORLD; p++)
+                if (p < a.world) __stcg(reinterpret_cast<uint2 *>(a.arena[p] + a.off_wn) + q, b);
+        }
+    }
+
+    // ---- 3. my slice is written everywhere; wait until every peer's is ----
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(&mine->finished[l], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last) {
+        if (threadIdx.x == 0) mine->finished[l] = 0u;
+        if ((int)threadIdx.x < a.world) {
+            Flags *peer = reinterpret_cast<Flags *>(a.arena[threadIdx.x]);
+            __threadfence_system();
+            st_release_sys(&peer->done[l][a.rank], a.seq);
+            while (ld_acquire_sys(&mine->done[l][threadIdx.x]) != a.seq) {
+            }
+        }
+    }
+}
+
+}  // namespace dp
+}  // namespace b2nn

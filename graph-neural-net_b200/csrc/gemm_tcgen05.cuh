@@ -42,8 +42,10 @@ constexpr int GEMM_CHUNK_BYTES = 64 * GEMM_BK * 2;      // one 64 x 64 TMA box: 
 constexpr int GEMM_A_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of A
 constexpr int GEMM_B_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of B (64 for a half tile)
 constexpr int GEMM_STAGE_BYTES = GEMM_A_BYTES + GEMM_B_BYTES;
-constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers, item ring*/;
 constexpr uint32_t GEMM_TMEM_COLS = 512;  // 2 accumulators x 256 fp32 columns
+constexpr int GEMM_SCHED_SLOTS = 4;       // depth of the work-item ring between the scheduler and the role warps
+constexpr int GEMM_SCHED_READERS = 2 /*producers*/ + 1 /*MMA*/ + 2 * GEMM_EPI_WARPS;
 
 enum EpiKind {
     EPI_ACT = 0,        // a = f(acc): store BF16 out0[M][ld0]
@@ -68,6 +70,7 @@ struct GemmArgs {
     float momentum;  // mu
     int act;
     float act_param;
+    unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
 };
 
 __device__ __forceinline__ float act_apply(int act, float p, float z) {
@@ -223,6 +226,31 @@ struct TileSched {
     }
 };
 
+// Dynamic work distribution.  A persistent kernel with a static tile list stalls on its slowest CTA, and any
+// kernel that shares SMs with it (the NCCL all-reduce, the side-stream update, the PCIe prologue) makes some
+// CTAs slow or late.  So pairs DRAW items from a global counter: the otherwise idle MMA warp of the peer CTA
+// (rank 1) is the pair's scheduler -- atomicAdd, publish the item into a 4-slot ring in BOTH CTAs' shared
+// memory (st.shared::cluster + cluster-scope mbarrier release/acquire), every role warp of the pair reads it
+// and releases the slot.  The pair that draws the last sentinel resets the counter for the next launch.
+struct SchedRing {
+    uint64_t *sfull, *sempty;      // [GEMM_SCHED_SLOTS]; sempty is only waited on in rank 1
+    volatile uint32_t *sitem;      // [GEMM_SCHED_SLOTS]
+    uint32_t sempty_rank1;         // shared::cluster address of rank 1's sempty[0]
+    int slot = 0;
+    uint32_t phase = 0;
+    int static_next = -1, static_stride = 0;  // static round-robin list instead (tile_counter == nullptr)
+    // warp-collective when whole_warp (epilogue warps), else called by one thread
+    __device__ __forceinline__ int next(bool whole_warp, int lane) {
+        if (static_stride) { const int it = static_next; static_next += static_stride; return it; }
+        ptx::mbar_wait_cluster(&sfull[slot], phase);
+        const int item = (int)sitem[slot];
+        if (whole_warp) __syncwarp();
+        if (!whole_warp || lane == 0) ptx::mbar_arrive_cluster(sempty_rank1 + 8u * (uint32_t)slot);
+        if (++slot == GEMM_SCHED_SLOTS) { slot = 0; phase ^= 1; }
+        return item;
+    }
+};
+
 // Barrier topology of the pair:
 //   full[s]    leader only, 1 arrival (its expect_tx of BOTH CTAs' bytes); both CTAs' TMA credit it
 //   empty[s]   one per CTA, signalled in both CTAs by the multicast tcgen05.commit
@@ -243,11 +271,17 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint64_t *tfull_bar = bars + 2 * GEMM_STAGES;
     uint64_t *tempty_bar = bars + 2 * GEMM_STAGES + 2;
     uint32_t *tmem_base_slot = reinterpret_cast<uint32_t *>(bars + 2 * GEMM_STAGES + 4);
+    SchedRing ring;
+    ring.sfull = bars + 2 * GEMM_STAGES + 5;
+    ring.sempty = ring.sfull + GEMM_SCHED_SLOTS;
+    ring.sitem = reinterpret_cast<volatile uint32_t *>(ring.sempty + GEMM_SCHED_SLOTS);
+    ring.sempty_rank1 = ptx::map_to_rank(ring.sempty, 1);
+    if (g.tile_counter == nullptr) { ring.static_next = (int)(blockIdx.x >> 1); ring.static_stride = (int)(gridDim.x >> 1); }
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int rank = (int)ptx::cluster_ctarank();
-    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int num_pairs = gridDim.x >> 1;
     const TileSched sched(g.M, g.N, num_pairs);
     const int k_blocks = (g.K + GEMM_BK - 1) / GEMM_BK;
 
@@ -261,6 +295,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         for (int a = 0; a < 2; a++) {
             ptx::mbar_init(&tfull_bar[a], 1);
             ptx::mbar_init(&tempty_bar[a], 2 * GEMM_EPI_WARPS);
+        }
+        for (int q = 0; q < GEMM_SCHED_SLOTS; q++) {
+            ptx::mbar_init(&ring.sfull[q], 1);
+            ptx::mbar_init(&ring.sempty[q], GEMM_SCHED_READERS);
         }
         ptx::fence_barrier_init();
     }
@@ -279,7 +317,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int item = pair; item < sched.total; item += num_pairs) {
+            for (int item = ring.next(false, 0); item < sched.total; item = ring.next(false, 0)) {
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
                 const int am0 = m0 + rank * GEMM_BM;        // this CTA's rows of A
@@ -313,7 +351,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             uint32_t acc_phase = 0;
             // bytes to step 16 along K inside a staged tile: 32 B in a K-major row, 16 rows of 128 B otherwise
             constexpr uint64_t a_kstep = (A_MN ? 2048 : 32) >> 4, b_kstep = (B_MN ? 2048 : 32) >> 4;
-            for (int item = pair; item < sched.total; item += num_pairs) {
+            for (int item = ring.next(false, 0); item < sched.total; item = ring.next(false, 0)) {
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
                 const uint32_t idesc = ptx::make_idesc_bf16(2 * GEMM_BM, bn, A_MN, B_MN);
@@ -338,6 +376,31 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 ptx::mma_commit_pair(&tfull_bar[acc]);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
+        } else if (rank == 1 && lane == 0 && g.tile_counter != nullptr) {
+            // ===================== scheduler of the pair (the peer's idle MMA warp) =====================
+            const uint32_t sitem0 = ptx::map_to_rank(const_cast<uint32_t *>(ring.sitem), 0);
+            const uint32_t sfull0 = ptx::map_to_rank(ring.sfull, 0);
+            int slot = 0;
+            uint32_t phase = 0;
+            bool first = true;
+            while (true) {
+                ptx::mbar_wait_cluster(&ring.sempty[slot], phase ^ 1);  // every reader is done with this slot
+                unsigned int item;
+                if (first) {  // the pair's first item needs no round trip to L2: items [0, num_pairs) are pre-assigned
+                    item = blockIdx.x >> 1;
+                    first = false;
+                } else {
+                    const unsigned int raw = atomicAdd(g.tile_counter, 1u);
+                    if (raw == (unsigned int)(sched.total - 1)) *g.tile_counter = 0u;  // last draw of all pairs
+                    item = raw + (unsigned int)num_pairs;
+                }
+                ring.sitem[slot] = item;
+                ptx::st_cluster_u32(sitem0 + 4u * (uint32_t)slot, item);
+                ptx::mbar_arrive_cluster(ptx::map_to_rank(&ring.sfull[slot], 1));
+                ptx::mbar_arrive_cluster(sfull0 + 8u * (uint32_t)slot);
+                if (item >= (unsigned int)sched.total) break;
+                if (++slot == GEMM_SCHED_SLOTS) { slot = 0; phase ^= 1; }
+            }
         }
     } else {
         // ===================== epilogue warps: each CTA drains its own 128 rows =====================
@@ -345,7 +408,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int part = (warp - 2) >> 2;       // which half of the tile's columns
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int item = pair; item < sched.total; item += num_pairs) {
+        for (int item = ring.next(true, lane); item < sched.total; item = ring.next(true, lane)) {
             int m0, n0, bn;
             sched.decode(item, m0, n0, bn);
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);

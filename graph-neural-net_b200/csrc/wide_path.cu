@@ -9,6 +9,7 @@
 #include "wide_path.hpp"
 
 #include "comm.hpp"
+#include "dp_kernels.cuh"
 #include "gemm_tcgen05.cuh"
 #include "wide_kernels.cuh"
 
@@ -48,6 +49,35 @@ int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t ro
     return B2NN_OK;
 }
 
+// measurement aid (B2NN_TRACE=1): remember a timing event on `st`
+void trace_mark(b2nn_net *net, cudaStream_t st, const char *label, int l) {
+    if (!net->trace || net->trace_marks.size() > 4000) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, st);
+    char buf[64];
+    snprintf(buf, sizeof buf, "%s%d", label, l);
+    net->trace_marks.emplace_back(e, buf);
+}
+void trace_dump(b2nn_net *net, int first, int count) {
+    if (!net->trace || net->trace_marks.empty()) return;
+    cudaStreamSynchronize(net->stream);
+    if (net->aux_stream) cudaStreamSynchronize(net->aux_stream);
+    // marks labelled "step<k>" delimit steps: print those of steps [first, first+count)
+    int step = -1;
+    cudaEvent_t base = nullptr;
+    for (auto &m : net->trace_marks) {
+        if (m.second.rfind("step", 0) == 0) { step++; if (step == first) base = m.first; }
+        if (step >= first && step < first + count && base) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, base, m.first);
+            fprintf(stderr, "[b2nn trace r%d] %8.3f %s\n", net->rank, ms, m.second.c_str());
+        }
+    }
+    for (auto &m : net->trace_marks) cudaEventDestroy(m.first);
+    net->trace_marks.clear();
+}
+
 // fold the recorded event pairs into the accumulators (synchronises the stream)
 int profile_flush(b2nn_net *net) {
     if (net->prof_used) {
@@ -81,7 +111,9 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     const int tiles = ((g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((g.N + GEMM_BN - 1) / GEMM_BN);
     const int max_pairs = net->num_sms / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
-    gemm_bf16_pair_kernel<EPI, A_MN, B_MN><<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, g);
+    GemmArgs ga = g;
+    ga.tile_counter = net->dynamic_tiles ? net->tile_counter : nullptr;
+    gemm_bf16_pair_kernel<EPI, A_MN, B_MN><<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
     if (net->profiling) {
         B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
         net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
@@ -105,6 +137,7 @@ static int launch_update(b2nn_net *net, WideLayer &y, float scale, float momentu
 
 int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity) {
     const int L = net->n_dims - 1;
+    if (net->aux_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->aux_stream));
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
         std::vector<float> tmp((size_t)y.in * y.ld_n, 0.f);
@@ -127,7 +160,19 @@ int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity) {
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
         std::vector<float> tmp((size_t)y.in * y.ld_n);
-        B2_CHECK_CUDA(cudaMemcpy(tmp.data(), velocity ? y.v : y.w, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        if (net->peer_arena.empty()) {
+            B2_CHECK_CUDA(cudaMemcpy(tmp.data(), velocity ? y.v : y.w, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        } else {
+            // optimizer state is sharded: slice p of the master weights / velocity lives on rank p
+            const long long n4 = (long long)y.in * y.ld_n / 4;
+            const size_t off = (size_t)((char *)(velocity ? y.v : y.w) - net->arena);
+            for (int p = 0; p < net->world; p++) {
+                const long long lo = (long long)p * n4 / net->world, hi = (long long)(p + 1) * n4 / net->world;
+                if (hi > lo)
+                    B2_CHECK_CUDA(cudaMemcpy(tmp.data() + 4 * lo, (const float *)(net->peer_arena[p] + off) + 4 * lo,
+                                             (size_t)(hi - lo) * 16, cudaMemcpyDefault));
+            }
+        }
         double *dst = w_flat + net->w_off[l];
         for (int i = 0; i < y.in; i++)
             for (int j = 0; j < y.out; j++) dst[(size_t)i * y.out + j] = (double)tmp[(size_t)i * y.ld_n + j];
@@ -145,6 +190,7 @@ static int prefer_max_shared_carveout() {
     if (done) return B2NN_OK;
     const int c = cudaSharedmemCarveoutMaxShared;
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::sgd_update, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(dp::reduce_update_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<double>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<float>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<__nv_bfloat16>,
@@ -162,29 +208,43 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
     const int L = net->n_dims - 1;
     B2_TRY(prefer_max_shared_carveout());
     net->wide.resize(L);
+    // One arena holds the cross-GPU flags and every layer's g / wn / w / v at the same offsets on every rank,
+    // so that a single CUDA IPC handle lets the peers of a data-parallel group address all of it (comm.cu).
+    auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+    size_t bytes = DP_FLAG_BYTES;
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
         y.in = net->dims[l]; y.out = net->dims[l + 1];
         y.ld_n = pad8(y.out);
         const size_t nf = (size_t)y.in * y.ld_n;
-        B2_CHECK_CUDA(cudaMalloc(&y.w, nf * sizeof(float)));
-        B2_CHECK_CUDA(cudaMalloc(&y.v, nf * sizeof(float)));
-        B2_CHECK_CUDA(cudaMemset(y.v, 0, nf * sizeof(float)));
-        B2_CHECK_CUDA(cudaMalloc(&y.wn, nf * sizeof(__nv_bfloat16)));
-        B2_CHECK_CUDA(cudaMemset(y.wn, 0, nf * sizeof(__nv_bfloat16)));
-        if (!net->fused_update) {
-            B2_CHECK_CUDA(cudaMalloc(&y.g, nf * sizeof(float)));
-            B2_CHECK_CUDA(cudaMemset(y.g, 0, nf * sizeof(float)));
-        }
+        bytes += 3 * up(nf * sizeof(float)) + up(nf * sizeof(__nv_bfloat16));
+    }
+    B2_CHECK_CUDA(cudaMalloc(&net->arena, bytes));
+    B2_CHECK_CUDA(cudaMemset(net->arena, 0, bytes));
+    net->arena_bytes = bytes;
+    size_t off = DP_FLAG_BYTES;
+    for (int l = 0; l < L; l++) {
+        WideLayer &y = net->wide[l];
+        const size_t nf = (size_t)y.in * y.ld_n;
+        y.g = (float *)(net->arena + off); off += up(nf * sizeof(float));
+        y.w = (float *)(net->arena + off); off += up(nf * sizeof(float));
+        y.v = (float *)(net->arena + off); off += up(nf * sizeof(float));
+        y.wn = (__nv_bfloat16 *)(net->arena + off); off += up(nf * sizeof(__nv_bfloat16));
         B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
     }
     // side stream: the HBM-bound update (and, data-parallel, the all-reduce before it) of layer l runs there
     // while the tensor cores go on with layer l-1's contractions
     B2_CHECK_CUDA(cudaStreamCreateWithFlags(&net->aux_stream, cudaStreamNonBlocking));
     net->layer_events.resize(L);
-    for (int l = 0; l < L; l++)
+    net->upd_done.resize(L);
+    net->upd_pending.assign(L, 0);
+    for (int l = 0; l < L; l++) {
         B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->layer_events[l], cudaEventDisableTiming));
+        B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->upd_done[l], cudaEventDisableTiming));
+    }
     B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->comm_done, cudaEventDisableTiming));
+    B2_CHECK_CUDA(cudaMalloc(&net->tile_counter, sizeof(unsigned int)));
+    B2_CHECK_CUDA(cudaMemset(net->tile_counter, 0, sizeof(unsigned int)));
     B2_CHECK_CUDA(cudaStreamCreateWithFlags(&net->copy_stream, cudaStreamNonBlocking));
     for (int q = 0; q < 2; q++) {
         B2_CHECK_CUDA(cudaEventCreateWithFlags(&net->slot_ready[q], cudaEventDisableTiming));
@@ -216,14 +276,18 @@ void wide_free(b2nn_net *net) {
     free_batch(net);
     for (auto e : net->layer_events) cudaEventDestroy(e);
     net->layer_events.clear();
+    for (auto e : net->upd_done) cudaEventDestroy(e);
+    net->upd_done.clear();
     if (net->comm_done) { cudaEventDestroy(net->comm_done); net->comm_done = nullptr; }
     if (net->aux_stream) { cudaStreamDestroy(net->aux_stream); net->aux_stream = nullptr; }
     if (net->copy_stream) { cudaStreamDestroy(net->copy_stream); net->copy_stream = nullptr; }
+    cudaFree(net->tile_counter); net->tile_counter = nullptr;
     for (int q = 0; q < 2; q++) {
         if (net->slot_ready[q]) { cudaEventDestroy(net->slot_ready[q]); net->slot_ready[q] = nullptr; }
         if (net->slot_free[q]) { cudaEventDestroy(net->slot_free[q]); net->slot_free[q] = nullptr; }
     }
-    for (auto &y : net->wide) { cudaFree(y.w); cudaFree(y.v); cudaFree(y.g); cudaFree(y.wn); }
+    cudaFree(net->arena);
+    net->arena = nullptr;
     net->wide.clear();
 }
 
@@ -322,6 +386,10 @@ int wide_forward(b2nn_net *net, int B) {
     const int L = net->n_dims - 1;
     for (int l = 0; l < L; l++) {
         WideLayer &y = net->wide[l];
+        if (net->upd_pending[l]) {  // layer l's update of the previous step may still be on the side stream
+            B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->upd_done[l], 0));
+            net->upd_pending[l] = 0;
+        }
         GemmArgs g{};
         g.M = B; g.N = y.out; g.K = y.in;
         g.act = net->inner_act; g.act_param = (float)net->inner_param;
@@ -332,6 +400,7 @@ int wide_forward(b2nn_net *net, int B) {
             g.out0 = b.logits; g.ld0 = pad8(y.out);
             B2_TRY((launch_gemm<EPI_LOGITS, false, true>(net, b.tm_a[l], y.tm_w, g)));
         }
+        trace_mark(net, net->stream, "fwd", l);
     }
     return B2NN_OK;
 }
@@ -352,48 +421,108 @@ int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev)
 // as the K dimension (S:279-283 + S:305-322: G_l = A_l^T . D_l+1, both operands MN-major) and the momentum
 // update (S:325-342) -- a streaming kernel after each gradient GEMM (or fused into its epilogue with
 // B2NN_FUSED_UPDATE=1); all-reduced per layer on a side stream first when data-parallel.
-int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
+static int launch_delta(b2nn_net *net, int l, int B) {
     WideBatch &b = net->wb;
-    const int L = net->n_dims - 1;
-    const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
-    bool side = false;
-    for (int l = L - 1; l >= 0; l--) {
-        WideLayer &y = net->wide[l];
-        if (l >= 1) {
-            GemmArgs g{};
-            g.M = B; g.N = y.in; g.K = y.out;
-            g.out0 = b.d[l]; g.ld0 = pad8(y.in);
-            g.aux = b.a[l]; g.ldaux = pad8(y.in);
-            g.act = net->inner_act; g.act_param = (float)net->inner_param;
-            B2_TRY((launch_gemm<EPI_DX, false, false>(net, b.tm_d[l + 1], y.tm_w, g)));
-        }
-        GemmArgs g{};
-        g.M = y.in; g.N = y.out; g.K = B;
-        g.ldw = y.ld_n;
-        if (net->world == 1 && net->fused_update) {
-            g.w = y.w; g.v = y.v;
-            g.out0 = y.wn; g.ld0 = y.ld_n;
-            g.scale = scale; g.momentum = (float)momentum;
-            B2_TRY((launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
-        } else {
-            g.w = y.g;
-            B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
-            // layer 0 has nothing left to overlap with on one GPU: update it in stream order
-            cudaStream_t us = (net->world > 1 || (l > 0 && net->overlap_update)) ? net->aux_stream : net->stream;
-            if (us != net->stream) {
-                B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
-                B2_CHECK_CUDA(cudaStreamWaitEvent(us, net->layer_events[l], 0));
-                side = true;
-            }
-            if (net->world > 1) B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, us));
-            B2_TRY(launch_update(net, y, scale, (float)momentum, 0, us));
-        }
+    WideLayer &y = net->wide[l];
+    GemmArgs g{};
+    g.M = B; g.N = y.in; g.K = y.out;
+    g.out0 = b.d[l]; g.ld0 = pad8(y.in);
+    g.aux = b.a[l]; g.ldaux = pad8(y.in);
+    g.act = net->inner_act; g.act_param = (float)net->inner_param;
+    B2_TRY((launch_gemm<EPI_DX, false, false>(net, b.tm_d[l + 1], y.tm_w, g)));
+    trace_mark(net, net->stream, "dX", l);
+    return B2NN_OK;
+}
+
+// gradient GEMM of layer l, then (all-reduce and) momentum update on stream `us`; when `us` is the side
+// stream, upd_pending[l] tells the next forward GEMM of layer l to wait for upd_done[l]
+static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, float momentum, cudaStream_t us) {
+    WideBatch &b = net->wb;
+    WideLayer &y = net->wide[l];
+    GemmArgs g{};
+    g.M = y.in; g.N = y.out; g.K = B;
+    g.ldw = y.ld_n;
+    if (net->world == 1 && net->fused_update) {
+        g.w = y.w; g.v = y.v;
+        g.out0 = y.wn; g.ld0 = y.ld_n;
+        g.scale = scale; g.momentum = momentum;
+        return launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g);
     }
-    if (side) {
-        B2_CHECK_CUDA(cudaEventRecord(net->comm_done, net->aux_stream));
-        B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->comm_done, 0));
+    g.w = y.g;
+    B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
+    trace_mark(net, net->stream, "dW", l);
+    if (us != net->stream) {
+        B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
+        B2_CHECK_CUDA(cudaStreamWaitEvent(us, net->layer_events[l], 0));
+    }
+    trace_mark(net, us, "  side:begin", l);
+    if (net->world > 1 && !net->peer_arena.empty()) {
+        // fused reduce-scatter + update + all-gather over NVLink peer memory (dp_kernels.cuh)
+        dp::Args a{};
+        for (int p = 0; p < net->world; p++) a.arena[p] = net->peer_arena[p];
+        a.world = net->world; a.rank = net->rank; a.layer = l;
+        a.off_g = (unsigned long long)((char *)y.g - net->arena); a.off_w = (unsigned long long)((char *)y.w - net->arena);
+        a.off_v = (unsigned long long)((char *)y.v - net->arena); a.off_wn = (unsigned long long)((char *)y.wn - net->arena);
+        a.n4 = (long long)y.in * y.ld_n / 4;
+        a.scale = scale; a.momentum = momentum;
+        a.seq = ++net->dp_seq;
+        long long blocks = (a.n4 / net->world + dp::DP_THREADS - 1) / dp::DP_THREADS;
+        if (blocks > net->dp_ctas) blocks = net->dp_ctas;
+        if (blocks < 1) blocks = 1;
+        dp::reduce_update_kernel<<<(int)blocks, dp::DP_THREADS, 0, us>>>(a);
+        net->launches++;
+        B2_CHECK_CUDA(cudaGetLastError());
+    } else {
+        if (net->world > 1) B2_TRY(comm_allreduce_sum_f32(net, y.g, (size_t)y.in * y.ld_n, us));
+        trace_mark(net, us, "  side:allreduced", l);
+        B2_TRY(launch_update(net, y, scale, momentum, 0, us));
+    }
+    trace_mark(net, us, "  side:updated", l);
+    if (us != net->stream) {
+        B2_CHECK_CUDA(cudaEventRecord(net->upd_done[l], us));
+        net->upd_pending[l] = 1;
     }
     return B2NN_OK;
+}
+
+// make the main stream wait for every update still running on the side stream
+int wide_join(b2nn_net *net) {
+    bool any = false;
+    for (size_t l = 0; l < net->upd_pending.size(); l++)
+        if (net->upd_pending[l]) {
+            B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->upd_done[l], 0));
+            net->upd_pending[l] = 0;
+            any = true;
+        }
+    (void)any;
+    return B2NN_OK;
+}
+
+// backward.  Deltas first, top-down (S:260-278: D_l = D_l+1 . W_l^T, both operands K-major; they need the
+// OLD weights), then the gradient GEMMs bottom-up with the batch sum as the K dimension (S:279-283 +
+// S:305-322: G_l = A_l^T . D_l+1, both operands MN-major), each followed on the side stream by its
+// all-reduce (data-parallel) and momentum update (S:325-342).  Bottom-up order puts the big early layers'
+// HBM / NVLink work under the remaining gradient GEMMs and leaves only the LAST (smallest) layer's exposed;
+// the next step's forward GEMM of layer l waits just for layer l's update (wide_forward).
+int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
+    const int L = net->n_dims - 1;
+    const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
+    const float mu = (float)momentum;
+    const bool side = net->world > 1 || net->overlap_update;
+    if (net->backward_reorder && !net->fused_update) {
+        for (int l = L - 1; l >= 1; l--) B2_TRY(launch_delta(net, l, B));
+        for (int l = 0; l < L; l++)
+            B2_TRY(launch_gradient_and_update(net, l, B, scale, mu, side ? net->aux_stream : net->stream));
+        return B2NN_OK;
+    }
+    // layer-by-layer order (the reference's own, S:262-284)
+    for (int l = L - 1; l >= 0; l--) {
+        if (l >= 1) B2_TRY(launch_delta(net, l, B));
+        // layer 0 has nothing left to overlap with on one GPU: update it in stream order
+        cudaStream_t us = (net->world > 1 || (l > 0 && net->overlap_update)) ? net->aux_stream : net->stream;
+        B2_TRY(launch_gradient_and_update(net, l, B, scale, mu, us));
+    }
+    return wide_join(net);
 }
 
 int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss) {

@@ -6,6 +6,8 @@ namespace b2nn {
 struct GemmArgs;
 int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld);
 int profile_flush(b2nn_net *net);
+void trace_mark(b2nn_net *net, cudaStream_t st, const char *label, int l);
+void trace_dump(b2nn_net *net, int first, int count);
 int wide_init(b2nn_net *net, const std::vector<double> &w_host);
 void wide_free(b2nn_net *net);
 int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity);
@@ -16,6 +18,7 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
                   int blocks_per_sm = 16);
 int wide_forward(b2nn_net *net, int B);
 int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev = nullptr);
+int wide_join(b2nn_net *net);
 int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum);
 int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss);
 int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,

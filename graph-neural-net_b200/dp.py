@@ -6,6 +6,8 @@ single-device gradient; the update divides by the GLOBAL batch size (S:333, `bat
 One process per GPU (torchrun); `torch.distributed` is plumbing only (rendezvous + shipping the
 NCCL unique id); the gradient all-reduce itself is issued by libb2nn.so on its own stream.
 """
+import os
+
 import numpy as np
 
 
@@ -41,4 +43,10 @@ def init_comm(net, dist, rank=None, world=None):
     uid = [commUniqueId() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     net.commInit(uid[0], rank, world)
+    if world > 1 and os.environ.get("B2NN_DP", "p2p") != "nccl":
+        # peer-memory path: all-gather the CUDA IPC handles of the parameter arenas (plumbing only)
+        handles = [None] * world
+        dist.all_gather_object(handles, net.commIpcExport())
+        net.commIpcImport(handles)
+        dist.barrier()
     return rank, world

@@ -187,6 +187,17 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_comm_init(self._h, buf, rank, world))
 
 
+    def commIpcExport(self):
+        buf = C.create_string_buffer(64)
+        capi.check(capi.lib().b2nn_comm_ipc_export(self._h, buf))
+        return buf.raw
+
+    def commIpcImport(self, handles):
+        blob = b"".join(bytes(h) for h in handles)
+        buf = C.create_string_buffer(blob, len(blob))
+        capi.check(capi.lib().b2nn_comm_ipc_import(self._h, buf, len(handles)))
+
+
 def commUniqueId():
     buf = C.create_string_buffer(128)
     capi.check(capi.lib().b2nn_comm_unique_id(buf))

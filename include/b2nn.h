@@ -175,6 +175,13 @@ int b2nn_sampler_destroy(b2nn_sampler *s);
 /* 128-byte NCCL unique id, created on rank 0 and shipped by the launcher */
 int b2nn_comm_unique_id(void *id128);
 int b2nn_comm_init(b2nn_net *net, const void *id128, int32_t rank, int32_t world);
+/* Peer-memory path (one process per GPU on one NVSwitch box): every rank exports a 64-byte CUDA IPC handle of
+ * its parameter arena, the launcher all-gathers them, every rank imports the [world][64] array.  After the
+ * import the per-layer NCCL all-reduce + update is replaced by ONE fused reduce-scatter / momentum update /
+ * all-gather kernel reading and writing the peers' memory over NVLink, with the optimizer state (master
+ * weights, velocity) sharded over the ranks; b2nn_get_weights / b2nn_get_velocity gather the shards. */
+int b2nn_comm_ipc_export(b2nn_net *net, void *handle64);
+int b2nn_comm_ipc_import(b2nn_net *net, const void *handles, int32_t world);
 
 /* ---- runtime -------------------------------------------------------------- */
 int b2nn_sync(b2nn_net *net);

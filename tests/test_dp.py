@@ -44,15 +44,19 @@ def test_gloo_world2_sharded_gradient_sum_equals_single_process(g, orc, tmp_path
 
 
 @pytest.mark.gpu
-def test_nccl_world2_matches_single_gpu(g, tmp_path):
-    """2 GPUs x 256 rows with the in-library NCCL all-reduce vs 1 GPU x 512 rows: replicas bit-identical,
-    weights equal to the single-GPU run within FP32 re-association of the batch sum (tolerance: 2e-3 of the
-    update's Frobenius norm per run of 6 steps; BF16 operands are identical, only the FP32 sum order differs)."""
+@pytest.mark.parametrize("mode", ["p2p", "nccl"])
+def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
+    """2 GPUs x 256 rows vs 1 GPU x 512 rows, with (p2p) the fused reduce-scatter/update/all-gather kernel over
+    NVLink peer memory and sharded optimizer state, and (nccl) the per-layer NCCL all-reduce + update: replicas
+    bit-identical, weights equal to the single-GPU run within FP32 re-association of the batch sum (tolerance:
+    2e-3 of the update's Frobenius norm per run of 6 steps; BF16 operands are identical, only the FP32 sum
+    order differs)."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
     from tests import dp_workers
+    monkeypatch.setenv("B2NN_DP", mode)
     mp.spawn(dp_workers.nccl_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
     r = np.load(tmp_path / "nccl.npz")
     assert int(r["replicas_equal"]) == 1
