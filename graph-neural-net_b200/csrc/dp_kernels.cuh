@@ -25,7 +25,10 @@ namespace b2nn {
 namespace dp {
 
 constexpr int MAX_LAYERS = 32;
-constexpr int DP_THREADS = 256;
+// Small CTAs on purpose: the kernel runs BESIDE the persistent GEMM (320 threads x up to 128 registers = 41 K of
+// the SM's 64 K registers); 128 threads x <= 96 registers fit next to it, a 256 x 172 CTA did not and the two
+// kernels time-shared the SMs (measured at 8 GPUs: the next forward GEMM took 2.6x longer).
+constexpr int DP_THREADS = 128;
 // layout of the flag block at the head of every arena (DP_FLAG_BYTES)
 struct Flags {
     unsigned int ready[MAX_LAYERS][DP_MAX_WORLD];  // [l][p]: rank p's gradient of layer l is complete (sequence number)
@@ -58,7 +61,7 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int *p) {
     return v;
 }
 
-__global__ void __launch_bounds__(DP_THREADS)
+__global__ void __launch_bounds__(DP_THREADS, 4)
 reduce_update_kernel(const Args a) {
     Flags *mine = reinterpret_cast<Flags *>(a.arena[a.rank]);
     const int l = a.layer;
@@ -89,7 +92,7 @@ reduce_update_kernel(const Args a) {
     float4 *v = reinterpret_cast<float4 *>(a.arena[a.rank] + a.off_v);
     const long long stride = (long long)gridDim.x * blockDim.x;
     // NVLink reads are latency-bound per request: keep UNROLL x world 16-byte loads in flight per thread
-    constexpr int UNROLL = 8;
+    constexpr int UNROLL = 4;
     for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += stride * UNROLL) {
         float4 g[UNROLL], wv[UNROLL], vv[UNROLL];
 #pragma unroll
