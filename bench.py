@@ -17,7 +17,6 @@ import argparse
 import json
 import os
 import sys
-import threading
 import time
 
 import numpy as np
@@ -67,40 +66,68 @@ def measured_peaks():
     return dict(tflops=1590.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
 
 
-class ClockSampler(threading.Thread):
-    """polls SM clock and clock-event reasons of one GPU while the timed regions run"""
+class ClockSampler:
+    """SM clock and clock-event reasons of one GPU while the timed regions run, sampled by a separate
+    `nvidia-smi -lms` PROCESS (the profiling recipe's clocks line): polling NVML from a thread of this process
+    takes driver locks that stall kernel launches and showed up as 3x outliers of the wall-clock e2e number."""
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
                0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
-        self.active = False
+        self.index, self.proc, self.active, self.t0 = index, None, False, None
+        self.windows = []
 
-    def run(self):
+    def start(self):
+        import subprocess
         try:
-            import pynvml
-            pynvml.nvmlInit()
-            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
-            while not self.stop_flag:
-                if self.active:
-                    self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
-                    try:
-                        r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
-                    except Exception:
-                        r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                    for bit, name in self.REASONS.items():
-                        if r & bit:
-                            self.reasons.add(name)
-                time.sleep(0.01)
-        except Exception as e:  # noqa
-            self.reasons.add("clock_sampling_failed: %s" % type(e).__name__)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=timestamp,clocks.sm,clocks.max.sm,"
+                 "clocks_event_reasons.active", "--format=csv,noheader,nounits", "-lms", "20"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def begin(self):
+        self.t0 = time.time()
+
+    def end(self):
+        if self.t0 is not None:
+            self.windows.append((self.t0, time.time()))
+            self.t0 = None
 
     def summary(self):
-        s = sorted(self.samples)
-        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "samples": len(s),
-                "reasons": sorted(self.reasons)}
+        import datetime
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["clock_sampling_unavailable"]}
+        time.sleep(0.05)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        clocks, reasons, mx, total = [], set(), None, 0
+        for line in out.splitlines():
+            f = [q.strip() for q in line.split(",")]
+            if len(f) < 4:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                mhz, mxv, mask = int(f[1]), int(f[2]), int(f[3], 16)
+            except Exception:
+                continue
+            total += 1
+            if not any(a - 0.02 <= ts <= b + 0.02 for a, b in self.windows):
+                continue
+            clocks.append(mhz)
+            mx = mxv
+            for bit, name in self.REASONS.items():
+                if mask & bit:
+                    reasons.add(name)
+        clocks.sort()
+        return {"sm_mhz": (clocks[len(clocks) // 2] if clocks else None), "sm_max_mhz": mx, "samples": len(clocks),
+                "samples_total": total, "reasons": sorted(reasons), "how": "nvidia-smi -lms 20 subprocess, samples "
+                "inside the timed regions (device-resident, roofline pass, e2e)"}
 
 
 def synth_data(rows, d0, n_classes, seed, dtype):
@@ -223,15 +250,16 @@ def run_b2nn(args):
         return float(t.item())
 
     # ---- device-resident timed region -----------------------------------------------------
-    sampler_thread.active = True
     train(ds_dev, idx_warm)
     barrier()
     l0 = net.kernelLaunches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler_thread.begin()
     ev0.record(stream)
     train(ds_dev, idx_time)
     ev1.record(stream)
     barrier()
+    sampler_thread.end()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = net.kernelLaunches() - l0
     value = world * B * K / (ms * 1e-3)
@@ -239,10 +267,16 @@ def run_b2nn(args):
     # ---- roofline pass: same K steps with event pairs around every contraction launch ------
     roof = None
     if bf16:
-        net.profileEnable(True)
+        net.profileEnable(True)   # side-stream work is serialised in this pass: each contraction is timed alone
+        sampler_thread.begin()
+        ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev2.record(stream)
         train(ds_dev, idx_time)
+        ev3.record(stream)
         gemm_ms, gemm_n, gemm_flops = net.profileRead()
+        sampler_thread.end()
         net.profileEnable(False)
+        prof_step_ms = ev2.elapsed_time(ev3) / K
         pk = measured_peaks()
         achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
         traffic = None
@@ -253,7 +287,8 @@ def run_b2nn(args):
         roof = {"bound": "tensor", "kernel": "gemm_bf16_pair_kernel (tcgen05 cta_group::2, all epilogues)", "achieved": achieved,
                 "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "peak_source": pk["src"],
                 "traffic": traffic, "launches": gemm_n, "avg_launch_ms": gemm_ms / max(gemm_n, 1),
-                "flops_per_step": float(B * flops_per_sample(dims)), "gemm_share_of_step": (gemm_ms / K) / (ms / K),
+                "flops_per_step": float(B * flops_per_sample(dims)),
+                "gemm_share_of_step": (gemm_ms / K) / prof_step_ms, "serialised_step_ms": prof_step_ms,
                 "step_tflops": world * B * flops_per_sample(dims) * K / (ms * 1e-3) / 1e12 / world}
     else:
         pk = measured_peaks()
@@ -277,10 +312,12 @@ def run_b2nn(args):
         ds_e2e = ds_dev
     train(ds_e2e, idx_warm[:min(3, idx_warm.shape[0])], want_loss=True)
     barrier()
+    sampler_thread.begin()
     t0 = time.perf_counter()
     losses = train(ds_e2e, idx_time, want_loss=True)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
+    sampler_thread.end()
     barrier()
     e2e = {"value": world * B * K / e2e_s, "unit": "samples/s",
            "h2d_bytes_per_step": (x_host_bytes if bf16 else 0) + B * 4, "d2h_bytes_per_step": 8,
@@ -290,8 +327,6 @@ def run_b2nn(args):
                     "(double-buffered under the previous step's GEMMs); per-step loss read back" if bf16 else
                     "b2nn_train_indexed over the device-resident dataMaster (784-wide rows live on the GPU like "
                     "the reference's in-memory HashMap); index lists cross PCIe every call")}
-    sampler_thread.active = False
-    sampler_thread.stop_flag = True
 
     # ---- the other headline config, quoted beside the main one --------------------------------
     also = None

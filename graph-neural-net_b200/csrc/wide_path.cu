@@ -508,7 +508,8 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
     const int L = net->n_dims - 1;
     const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
     const float mu = (float)momentum;
-    const bool side = net->world > 1 || net->overlap_update;
+    // with b2nn_profile_enable on, everything runs in stream order so that the event pairs time each contraction alone
+    const bool side = (net->world > 1 || net->overlap_update) && !net->profiling;
     if (net->backward_reorder && !net->fused_update) {
         for (int l = L - 1; l >= 1; l--) B2_TRY(launch_delta(net, l, B));
         for (int l = 0; l < L; l++)
