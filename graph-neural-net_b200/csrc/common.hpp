@@ -169,7 +169,7 @@ struct b2nn_net {
     char *arena = nullptr;           // flags + all layers' g / w / v / wn (one allocation, one IPC handle)
     size_t arena_bytes = 0;
     std::vector<char *> peer_arena;  // [world] peers' arenas mapped with CUDA IPC (own entry = arena); empty: NCCL path
-    int dp_ctas = 296;                // CTAs of the fused reduce/update kernel (B2NN_DP_CTAS)
+    int dp_ctas = 0;                  // CTAs of the fused reduce/update kernel (B2NN_DP_CTAS)
     unsigned int dp_seq = 0;         // sequence number of the cross-GPU flag handshakes
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;

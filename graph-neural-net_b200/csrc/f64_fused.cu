@@ -1,6 +1,7 @@
 // f64_fused.cu -- host side of K1, the persistent fused FP64 training kernel (f64_fused.cuh).
 #include "f64_fused.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "f64_path.hpp"
@@ -105,10 +106,26 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     p.bulk = Xu8 ? (d0 % 16 == 0) : (d0 % 2 == 0);
     if (getenv("B2NN_F64_NO_BULK")) p.bulk = 0;
     B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, sizeof(unsigned long long), net->stream));
+    static unsigned long long *prof_dev = nullptr;
+    const bool prof = getenv("B2NN_K1_PROF") != nullptr;
+    if (prof) {
+        if (!prof_dev) B2_CHECK_CUDA(cudaMalloc(&prof_dev, 8 * sizeof(unsigned long long)));
+        B2_CHECK_CUDA(cudaMemsetAsync(prof_dev, 0, 8 * sizeof(unsigned long long), net->stream));
+    }
+    p.prof = prof ? prof_dev : nullptr;
     void *args[] = {(void *)&p};
     B2_CHECK_CUDA(cudaLaunchCooperativeKernel(fused_kernel_for(net->inner_act), dim3(G), dim3(512), args,
                                               lo.smem_bytes, net->stream));
     net->launches++;
+    if (prof) {
+        unsigned long long h[8];
+        B2_CHECK_CUDA(cudaMemcpyAsync(h, prof_dev, sizeof h, cudaMemcpyDeviceToHost, net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        const char *names[8] = {"stage", "phase1", "barrier1", "phase2", "barrier2", "phase3", "phase4", "phase5"};
+        fprintf(stderr, "[b2nn K1 prof] cycles per step (CTA 0):");
+        for (int i = 0; i < 8; i++) fprintf(stderr, " %s %.0f", names[i], (double)h[i] / iters);
+        fprintf(stderr, "\n");
+    }
     return B2NN_OK;
 }
 

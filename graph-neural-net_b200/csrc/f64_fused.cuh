@@ -46,6 +46,7 @@ struct FusedParams {
     int o_w2t;  // [d3][d2] transposed copy of W2 for the delta2 pass
     int o_lut, o_stage, o_mbar;  // 256-entry f(byte/255) table, byte staging for one batch, mbarrier
     int bulk;                    // rows can be fetched with cp.async.bulk (16-byte aligned rows)
+    unsigned long long *prof;    // optional [8] cycle sums per phase (CTA 0), measurement aid (B2NN_K1_PROF=1)
 };
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -157,6 +158,13 @@ __device__ __forceinline__ void issue_batch_fetch(const FusedParams &p, int it, 
     }
 }
 
+#define K1_MARK(i)                                                      \
+    if (p.prof != nullptr && c == 0 && tid == 0) {                      \
+        const long long now_ = clock64();                               \
+        p.prof[i] += (unsigned long long)(now_ - tprev_);               \
+        tprev_ = now_;                                                  \
+    }
+
 template <int IACT>
 __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p) {
     extern __shared__ double sm[];
@@ -217,6 +225,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     if (p.bulk && tid == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar);
 
     unsigned long long bar_target = 0;
+    long long tprev_ = clock64();
     for (int it = 0; it < p.iters; it++) {
         const int32_t *idx = p.idx + (size_t)it * B;
         double *z1pub = p.z1buf + (size_t)(it & 1) * B * d1;
@@ -265,6 +274,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         // the byte staging buffer is free again: fetch the NEXT batch while this step computes
         if (p.bulk && u8 && tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar);
 
+        K1_MARK(0)  // batch staged
         // ---- phase 1: z1[:, own columns] = a0 . W0[:, own]; publish ----
         blocked_dot(a0, w0, B, d0, nc0, part, warp, lane, NW);
         if (have_next) {
@@ -284,8 +294,10 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             a1o[b * ncm + jj] = act(IACT, p.inner_p, z);
             z1pub[(size_t)b * d1 + j0 + jj] = z;
         }
+        K1_MARK(1)  // phase 1
         bar_target += G;
         grid_barrier(p.bar, bar_target);
+        K1_MARK(2)  // barrier 1
 
         // ---- phase 2: owners of W1 columns: a1 = f(z1) (all of it), z2[:, own] = a1 . W1[:, own]; publish ----
         if (nc1 > 0) {
@@ -312,8 +324,10 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 z2pub[(size_t)b * d2 + k0 + kk] = z;
             }
         }
+        K1_MARK(3)  // phase 2
         bar_target += G;
         grid_barrier(p.bar, bar_target);
+        K1_MARK(4)  // barrier 2
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
         {
@@ -386,14 +400,20 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         }
         __syncthreads();
-        if (p.loss_out && c == 0 && tid == 0) {
-            double tot = 0.0;
-            for (int b = 0; b < B; b++) {
+        if (p.loss_out && c == 0) {
+            // per-row loss in ascending j (one thread per row), then the batch sum in ascending b: the same
+            // order of additions as a single serial loop
+            if (tid < B) {
                 double l = 0.0;
-                for (int j = 0; j < d3; j++) l = __dsub_rn(l, z3[b * d3 + j]);
-                tot = __dadd_rn(tot, l);
+                for (int j = 0; j < d3; j++) l = __dsub_rn(l, z3[tid * d3 + j]);
+                misc[tid] = l;
             }
-            p.loss_out[it] = tot;
+            __syncthreads();
+            if (tid == 0) {
+                double tot = 0.0;
+                for (int b = 0; b < B; b++) tot = __dadd_rn(tot, misc[b]);
+                p.loss_out[it] = tot;
+            }
         }
         // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
         for (int b = warp; b < B; b += NW)
@@ -404,6 +424,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         __syncthreads();
 
+        K1_MARK(5)  // phase 3
         // ---- phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own) ----
         for (int e = tid; e < B * nc0; e += NT) {
             const int b = e / nc0, jj = e - b * nc0;
@@ -419,6 +440,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         __syncthreads();
 
+        K1_MARK(6)  // phase 4
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
         for (int k = tid; k < d0; k += NT) {
@@ -482,6 +504,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             v2[e] = adj;
         }
         __syncthreads();
+        K1_MARK(7)  // phase 5
     }
 
     // ---- write the CTA's slices back to the canonical [in][out] state ----
