@@ -132,40 +132,73 @@ __device__ __forceinline__ void store_f32_row(float *base, int ld, int N, int m,
     }
 }
 
+// x[c] = acc[c] * fprime(a[c]) for 32 columns, a unpacked from BF16 on the fly
+template <class F>
+__device__ __forceinline__ void dx32(const uint4 (&u)[4], const uint32_t (&r)[32], float (&x)[32], F fprime) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u[q]);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const float2 a = __bfloat1622float2(h[e]);
+            x[8 * q + 2 * e] = __uint_as_float(r[8 * q + 2 * e]) * fprime(a.x);
+            x[8 * q + 2 * e + 1] = __uint_as_float(r[8 * q + 2 * e + 1]) * fprime(a.y);
+        }
+    }
+}
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0, const uint32_t (&r)[32]) {
     if (m >= g.M || n0 >= g.N) return;
     if constexpr (EPI == EPI_ACT) {
         float x[32];
 #pragma unroll
-        for (int c = 0; c < 32; c++) x[c] = act_apply(g.act, g.act_param, __uint_as_float(r[c]));
+        for (int c = 0; c < 32; c++) x[c] = __uint_as_float(r[c]);
+        // branch on the activation once per 32 columns, not per element (fewer live registers)
+        switch (g.act) {
+        case ACT_LEAKY_RELU:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = x[c] > 0.f ? x[c] : g.act_param * x[c];
+            break;
+        case ACT_RELU:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = fmaxf(x[c], 0.f);
+            break;
+        case ACT_SIGMOID:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = 1.f / (1.f + __expf(-x[c]));
+            break;
+        case ACT_TANH:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = 1.f - 2.f / (1.f + __expf(2.f * x[c]));  // tanh, BF16-accurate
+            break;
+        default: break;  // identity
+        }
         store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_LOGITS) {
         store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, r);
     } else if constexpr (EPI == EPI_DX) {
         const __nv_bfloat16 *arow = g.aux + (size_t)m * g.ldaux + n0;
-        float x[32];
+        uint4 u[4];  // the 32 stored activations a = f(z), packed BF16
         if (n0 + 32 <= g.N) {
-            uint4 u[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) u[q] = reinterpret_cast<const uint4 *>(arow)[q];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u[q]);
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    float2 a = __bfloat1622float2(h[e]);
-                    x[8 * q + 2 * e] = __uint_as_float(r[8 * q + 2 * e]) * act_prime_from_a(g.act, g.act_param, a.x);
-                    x[8 * q + 2 * e + 1] =
-                        __uint_as_float(r[8 * q + 2 * e + 1]) * act_prime_from_a(g.act, g.act_param, a.y);
-                }
-            }
         } else {
+            uint32_t *uw = reinterpret_cast<uint32_t *>(u);
 #pragma unroll
-            for (int c = 0; c < 32; c++) {
-                float a = (n0 + c < g.N) ? __bfloat162float(arow[c]) : 0.f;
-                x[c] = __uint_as_float(r[c]) * act_prime_from_a(g.act, g.act_param, a);
+            for (int c = 0; c < 32; c += 2) {
+                const float lo = (n0 + c < g.N) ? __bfloat162float(arow[c]) : 0.f;
+                const float hi = (n0 + c + 1 < g.N) ? __bfloat162float(arow[c + 1]) : 0.f;
+                uw[c >> 1] = pack_bf16x2(lo, hi);
             }
+        }
+        float x[32];
+        switch (g.act) {  // one branch per 32 columns; f' from the stored activation
+        case ACT_LEAKY_RELU: { const float p = g.act_param; dx32(u, r, x, [p](float a) { return a > 0.f ? 1.f : p; }); break; }
+        case ACT_RELU: dx32(u, r, x, [](float a) { return a > 0.f ? 1.f : 0.f; }); break;
+        case ACT_SIGMOID: dx32(u, r, x, [](float a) { return a * (1.f - a); }); break;
+        case ACT_TANH: dx32(u, r, x, [](float a) { return 1.f - a * a; }); break;
+        default: dx32(u, r, x, [](float) { return 1.f; });
         }
         store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_DW_UPDATE) {
