@@ -351,6 +351,7 @@ def run_b2nn(args):
             "dtype": wl["prec"], "data": "synthetic",
             "config": {"workload": args.workload + ": " + wl["desc"], "dims": dims, "batch_per_gpu": B,
                        "global_batch": B * world, "parallelism": "dp%d" % world,
+                       "exchange": net.commMode() if bf16 else "single",
                        "l2": "no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh "
                              "batch, larger than the 126 MB L2" % (n_weights(dims) * 12 / 1e6) if bf16 else
                              "state is L2-resident by design (4.3 MB); batches cycle through 60000 rows (376 MB)"},

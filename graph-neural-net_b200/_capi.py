@@ -48,6 +48,11 @@ SIGNATURES = {
     "b2nn_comm_init": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32]),
     "b2nn_comm_ipc_export": (C.c_int, [_vp, _vp]),
     "b2nn_comm_ipc_import": (C.c_int, [_vp, _vp, C.c_int32]),
+    "b2nn_comm_nvls_export": (C.c_int, [_vp, _vp]),
+    "b2nn_comm_nvls_import": (C.c_int, [_vp, _vp, C.c_int32]),
+    "b2nn_comm_nvls_team": (C.c_int, [_vp, _vp]),
+    "b2nn_comm_nvls_bind": (C.c_int, [_vp]),
+    "b2nn_comm_mode": (C.c_int, [_vp, _vp]),
     "b2nn_sync": (C.c_int, [_vp]),
     "b2nn_set_stream": (C.c_int, [_vp, _vp]),
     "b2nn_kernel_launches": (C.c_int, [_vp, _lp]),

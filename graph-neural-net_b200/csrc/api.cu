@@ -254,4 +254,39 @@ int b2nn_comm_ipc_import(b2nn_net *net, const void *handles, int32_t world) {
     return comm_ipc_import(net, handles, world);
 }
 
+int b2nn_comm_nvls_export(b2nn_net *net, int32_t *pid_fd) {
+    B2_REQUIRE(net != nullptr && pid_fd != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    return comm_vmm_export(net, &pid_fd[0], &pid_fd[1]);
+}
+
+int b2nn_comm_nvls_import(b2nn_net *net, const int32_t *pid_fd, int32_t world) {
+    B2_REQUIRE(net != nullptr && pid_fd != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_REQUIRE(world >= 1 && world <= DP_MAX_WORLD, B2NN_ERR_INVALID_ARG, "bad world %d", world);
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    int32_t pids[DP_MAX_WORLD], fds[DP_MAX_WORLD];
+    for (int p = 0; p < world; p++) { pids[p] = pid_fd[2 * p]; fds[p] = pid_fd[2 * p + 1]; }
+    return comm_vmm_import(net, pids, fds, world);
+}
+
+int b2nn_comm_nvls_team(b2nn_net *net, int32_t *pid_fd) {
+    B2_REQUIRE(net != nullptr && pid_fd != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    if (net->rank == 0) B2_TRY(comm_mc_create(net, &pid_fd[0], &pid_fd[1]));
+    else B2_TRY(comm_mc_import(net, pid_fd[0], pid_fd[1]));
+    return comm_mc_add_device(net);
+}
+
+int b2nn_comm_mode(const b2nn_net *net, int32_t *mode) {
+    B2_REQUIRE(net != nullptr && mode != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    *mode = net->world <= 1 ? 0 : net->peer_arena.empty() ? 1 : net->use_multimem ? 3 : 2;
+    return B2NN_OK;
+}
+
+int b2nn_comm_nvls_bind(b2nn_net *net) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    return comm_mc_bind(net);
+}
+
 }  // extern "C"

@@ -138,6 +138,7 @@ int comm_ipc_import(b2nn_net *net, const void *handles, int world) {
 }
 
 void comm_destroy(b2nn_net *net) {
+    if (net->vmm_arena) comm_vmm_destroy(net);  // also forgets the (non-IPC) peer mappings
     for (size_t p = 0; p < net->peer_arena.size(); p++)
         if ((int)p != net->rank && net->peer_arena[p]) cudaIpcCloseMemHandle(net->peer_arena[p]);
     net->peer_arena.clear();

@@ -170,6 +170,14 @@ struct b2nn_net {
     size_t arena_bytes = 0;
     std::vector<char *> peer_arena;  // [world] peers' arenas mapped with CUDA IPC (own entry = arena); empty: NCCL path
     int dp_ctas = 0;                  // CTAs of the fused reduce/update kernel (B2NN_DP_CTAS)
+    // NVSwitch multicast path (comm_vmm.cu): arena re-allocated with cuMemCreate, bound to a multicast object
+    bool vmm_arena = false;
+    CUmemGenericAllocationHandle vmm_handle = 0, mc_handle = 0;
+    size_t vmm_bytes = 0, vmm_gran = 0;
+    int vmm_fd = -1, mc_fd = -1;
+    bool use_multimem = false;       // exchange kernel uses multimem.ld_reduce / multimem.st through mc_base
+    char *mc_base = nullptr;         // multicast mapping of all ranks' arenas (multimem.* addresses)
+    std::vector<CUmemGenericAllocationHandle> peer_handles;
     unsigned int dp_seq = 0;         // sequence number of the cross-GPU flag handshakes
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;

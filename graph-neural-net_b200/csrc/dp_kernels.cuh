@@ -40,6 +40,7 @@ static_assert(sizeof(Flags) <= DP_FLAG_BYTES, "flag block does not fit");
 
 struct Args {
     char *arena[DP_MAX_WORLD];  // every rank's arena (own entry included), same layout everywhere
+    char *mc;                   // multicast mapping of all arenas (NVSwitch), or null: plain peer loads / stores
     int world, rank, layer;
     unsigned long long off_g, off_w, off_v, off_wn;  // byte offsets of this layer's arrays inside an arena
     long long n4;               // float4 elements of the layer (padded [in][ld_n] array)
@@ -59,6 +60,20 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int *p) {
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
+}
+
+// 16 bytes summed over every GPU of the multicast team inside the switch
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const void *mc_addr) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(mc_addr)
+                 : "memory");
+    return v;
+}
+// 8 bytes (four BF16) replicated into every GPU of the team by the switch
+__device__ __forceinline__ void multimem_st_bf16x4(void *mc_addr, uint2 b) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc_addr), "r"(b.x), "r"(b.y) : "memory");
 }
 
 __global__ void __launch_bounds__(DP_THREADS, 4)
@@ -97,6 +112,15 @@ reduce_update_kernel(const Args a) {
         float4 g[UNROLL], wv[UNROLL], vv[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.mc != nullptr) {
+            // in-switch reduction: ONE load per owned float4, the NVSwitch gathers and adds the G copies
+            const float4 *gm = reinterpret_cast<const float4 *>(a.mc + a.off_g);
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                const long long q = q0 + u * stride;
+                if (q < hi) g[u] = multimem_ld_reduce_add(gm + q);
+            }
+        } else
 #pragma unroll
         for (int p = 0; p < DP_MAX_WORLD; p++) {
             if (p < a.world) {
@@ -127,9 +151,13 @@ reduce_update_kernel(const Args a) {
             v[q] = V;
             w[q] = W;
             const uint2 b = make_uint2(pack_bf16x2(W.x, W.y), pack_bf16x2(W.z, W.w));
+            if (a.mc != nullptr) {
+                multimem_st_bf16x4(reinterpret_cast<uint2 *>(a.mc + a.off_wn) + q, b);  // one store, G copies
+            } else {
 #pragma unroll
-            for (int p = 0; p < DP_MAX_WORLD; p++)
-                if (p < a.world) __stcg(reinterpret_cast<uint2 *>(a.arena[p] + a.off_wn) + q, b);
+                for (int p = 0; p < DP_MAX_WORLD; p++)
+                    if (p < a.world) __stcg(reinterpret_cast<uint2 *>(a.arena[p] + a.off_wn) + q, b);
+            }
         }
     }
 

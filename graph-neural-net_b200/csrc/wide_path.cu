@@ -253,6 +253,20 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
     return wide_upload_weights(net, w_host.data(), false);
 }
 
+// the arena moved (comm_vmm.cu): every layer pointer is an offset from its base; the operand maps hold addresses
+int wide_rebase_arena(b2nn_net *net, char *new_base) {
+    char *old = net->arena;
+    for (auto &y : net->wide) {
+        y.g = (float *)(new_base + ((char *)y.g - old));
+        y.w = (float *)(new_base + ((char *)y.w - old));
+        y.v = (float *)(new_base + ((char *)y.v - old));
+        y.wn = (__nv_bfloat16 *)(new_base + ((char *)y.wn - old));
+        B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
+    }
+    net->arena = new_base;
+    return B2NN_OK;
+}
+
 static void free_batch(b2nn_net *net) {
     WideBatch &b = net->wb;
     if (!b.a.empty()) b.a[0] = nullptr;  // alias of a slot
@@ -286,7 +300,7 @@ void wide_free(b2nn_net *net) {
         if (net->slot_ready[q]) { cudaEventDestroy(net->slot_ready[q]); net->slot_ready[q] = nullptr; }
         if (net->slot_free[q]) { cudaEventDestroy(net->slot_free[q]); net->slot_free[q] = nullptr; }
     }
-    cudaFree(net->arena);
+    if (net->arena && !net->vmm_arena) cudaFree(net->arena);
     net->arena = nullptr;
     net->wide.clear();
 }
@@ -460,6 +474,7 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
         // fused reduce-scatter + update + all-gather over NVLink peer memory (dp_kernels.cuh)
         dp::Args a{};
         for (int p = 0; p < net->world; p++) a.arena[p] = net->peer_arena[p];
+        a.mc = net->use_multimem ? net->mc_base : nullptr;
         a.world = net->world; a.rank = net->rank; a.layer = l;
         a.off_g = (unsigned long long)((char *)y.g - net->arena); a.off_w = (unsigned long long)((char *)y.w - net->arena);
         a.off_v = (unsigned long long)((char *)y.v - net->arena); a.off_wn = (unsigned long long)((char *)y.wn - net->arena);

@@ -8,6 +8,7 @@ int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t ro
 int profile_flush(b2nn_net *net);
 void trace_mark(b2nn_net *net, cudaStream_t st, const char *label, int l);
 void trace_dump(b2nn_net *net, int first, int count);
+int wide_rebase_arena(b2nn_net *net, char *new_base);
 int wide_init(b2nn_net *net, const std::vector<double> &w_host);
 void wide_free(b2nn_net *net);
 int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity);

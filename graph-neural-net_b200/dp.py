@@ -43,10 +43,39 @@ def init_comm(net, dist, rank=None, world=None):
     uid = [commUniqueId() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     net.commInit(uid[0], rank, world)
-    if world > 1 and os.environ.get("B2NN_DP", "p2p") != "nccl":
+    # B2NN_DP = nvls | p2p | nccl.  Default: the in-switch reduction from 4 GPUs up (measured at 8 GPUs: step
+    # 0.769 ms against 0.848 ms for plain peer memory), plain peer memory at 2 (there multimem sends the local
+    # half through the switch as well: 0.799 against 0.768 ms).  profiles/r01_scaling.md has the runs.
+    mode = os.environ.get("B2NN_DP") or ("nvls" if world >= 4 else "p2p")
+    if world > 1 and mode == "nvls":
+        if _init_nvls(net, dist, rank, world):
+            return rank, world
+        mode = "p2p"  # no multicast on this box: nothing was changed, use plain peer memory
+    if world > 1 and mode != "nccl":
         # peer-memory path: all-gather the CUDA IPC handles of the parameter arenas (plumbing only)
         handles = [None] * world
         dist.all_gather_object(handles, net.commIpcExport())
         net.commIpcImport(handles)
         dist.barrier()
     return rank, world
+
+
+def _init_nvls(net, dist, rank, world):
+    """NVSwitch multicast set-up (include/b2nn.h, b2nn_comm_nvls_*): only (pid, fd) pairs travel through
+    the process group.  False (on every rank) when any rank lacks multicast support."""
+    mine = net.commNvlsExport()
+    pairs = [None] * world
+    dist.all_gather_object(pairs, mine)
+    if any(p is None for p in pairs):
+        if mine is not None:
+            raise RuntimeError("multicast support differs between ranks")
+        return False
+    net.commNvlsImport(pairs)
+    team = [net.commNvlsTeam(None) if rank == 0 else None]
+    dist.broadcast_object_list(team, src=0)   # rank 0 keeps its fd open until everybody has duplicated it
+    if rank != 0:
+        net.commNvlsTeam(team[0])
+    dist.barrier()                            # every device joined the team
+    net.commNvlsBind()
+    dist.barrier()
+    return True

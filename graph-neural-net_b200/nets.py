@@ -197,6 +197,34 @@ class NeuralNet:
         buf = C.create_string_buffer(blob, len(blob))
         capi.check(capi.lib().b2nn_comm_ipc_import(self._h, buf, len(handles)))
 
+    def commNvlsExport(self):
+        """-> (pid, fd) of this rank's arena, or None when the device / driver has no multicast support"""
+        pf = (C.c_int32 * 2)()
+        rc = capi.lib().b2nn_comm_nvls_export(self._h, pf)
+        if rc == capi.ERR_UNSUPPORTED:
+            return None
+        capi.check(rc)
+        return int(pf[0]), int(pf[1])
+
+    def commNvlsImport(self, pid_fds):
+        flat = (C.c_int32 * (2 * len(pid_fds)))(*[int(x) for pf in pid_fds for x in pf])
+        capi.check(capi.lib().b2nn_comm_nvls_import(self._h, flat, len(pid_fds)))
+
+    def commNvlsTeam(self, pid_fd=None):
+        """rank 0: pid_fd None -> returns the multicast object's (pid, fd); others pass rank 0's pair"""
+        pf = (C.c_int32 * 2)(*(pid_fd or (0, 0)))
+        capi.check(capi.lib().b2nn_comm_nvls_team(self._h, pf))
+        return int(pf[0]), int(pf[1])
+
+    def commMode(self):
+        """'single' | 'nccl' | 'p2p' | 'nvls' -- the gradient exchange the next step uses"""
+        m = C.c_int32()
+        capi.check(capi.lib().b2nn_comm_mode(self._h, C.byref(m)))
+        return ("single", "nccl", "p2p", "nvls")[m.value]
+
+    def commNvlsBind(self):
+        capi.check(capi.lib().b2nn_comm_nvls_bind(self._h))
+
 
 def commUniqueId():
     buf = C.create_string_buffer(128)

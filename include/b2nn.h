@@ -182,6 +182,22 @@ int b2nn_comm_init(b2nn_net *net, const void *id128, int32_t rank, int32_t world
  * weights, velocity) sharded over the ranks; b2nn_get_weights / b2nn_get_velocity gather the shards. */
 int b2nn_comm_ipc_export(b2nn_net *net, void *handle64);
 int b2nn_comm_ipc_import(b2nn_net *net, const void *handles, int32_t world);
+/* NVSwitch multicast variant of the peer-memory path (instead of the two IPC calls): the fused kernel then sums the
+ * gradient INSIDE the switch (multimem.ld_reduce) and replicates the new BF16 weights with one multimem.st.
+ * The arena moves into a cuMemCreate allocation shared by POSIX file descriptor; the launcher carries
+ * (pid, fd) pairs between the ranks and the library duplicates them with pidfd_getfd.  Sequence, all ranks:
+ *   export(pid_fd) -> all-gather -> import(all [world][2]) ->
+ *   team(pid_fd): rank 0 creates the multicast object and RETURNS its (pid, fd); the launcher broadcasts it; the
+ *                 other ranks pass it IN; every rank joins the team ->
+ *   barrier -> bind() -> barrier.
+ * B2NN_ERR_UNSUPPORTED from export (no multicast on this device / driver) leaves the net untouched. */
+int b2nn_comm_nvls_export(b2nn_net *net, int32_t *pid_fd);
+int b2nn_comm_nvls_import(b2nn_net *net, const int32_t *pid_fd, int32_t world);
+int b2nn_comm_nvls_team(b2nn_net *net, int32_t *pid_fd);
+int b2nn_comm_nvls_bind(b2nn_net *net);
+/* which exchange the next gradient step uses: 0 single GPU, 1 NCCL all-reduce + update, 2 fused kernel over peer
+ * memory, 3 fused kernel with in-switch reduction (multicast) */
+int b2nn_comm_mode(const b2nn_net *net, int32_t *mode);
 
 /* ---- runtime -------------------------------------------------------------- */
 int b2nn_sync(b2nn_net *net);

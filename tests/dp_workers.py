@@ -95,6 +95,6 @@ def nccl_worker(rank, world, port, out_dir):
         for it in range(iters):
             single.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu)
         np.savez(os.path.join(out_dir, "nccl.npz"), w_dp=w, w_single=single.getWeights(), w0=w0,
-                 replicas_equal=int(flag.item()), launches=net.kernelLaunches())
+                 replicas_equal=int(flag.item()), launches=net.kernelLaunches(), mode=net.commMode())
     dist.barrier()
     dist.destroy_process_group()

@@ -44,9 +44,11 @@ def test_gloo_world2_sharded_gradient_sum_equals_single_process(g, orc, tmp_path
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["p2p", "nccl"])
+@pytest.mark.parametrize("mode", ["p2p", "nccl", "nvls"])
 def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
-    """2 GPUs x 256 rows vs 1 GPU x 512 rows, with (p2p) the fused reduce-scatter/update/all-gather kernel over
+    """2 GPUs x 256 rows vs 1 GPU x 512 rows, with (nvls) the fused kernel summing inside the NVSwitch
+    (multimem.ld_reduce) and replicating the weights with multimem.st -- falls back to p2p where the box has
+    no multicast support --, (p2p) the fused reduce-scatter/update/all-gather kernel over
     NVLink peer memory and sharded optimizer state, and (nccl) the per-layer NCCL all-reduce + update: replicas
     bit-identical, weights equal to the single-GPU run within FP32 re-association of the batch sum (tolerance:
     2e-3 of the update's Frobenius norm per run of 6 steps; BF16 operands are identical, only the FP32 sum
@@ -64,3 +66,5 @@ def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
     rel = np.linalg.norm(du_dp - du_1) / np.linalg.norm(du_1)
     assert rel < 2e-3, rel
     assert int(r["launches"]) > 0
+    assert str(r["mode"]) in ((mode, "p2p") if mode == "nvls" else (mode,))
+    print("exchange:", str(r["mode"]))
