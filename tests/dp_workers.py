@@ -59,6 +59,59 @@ def gloo_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
+class _RecordingNet:
+    """stands in for a device net: records the order of the b2nn_comm_* calls init_comm makes"""
+
+    def __init__(self, rank, multicast):
+        self.rank, self.multicast, self.calls = rank, multicast, []
+
+    def commInit(self, uid, rank, world):
+        self.calls.append(("init", bytes(uid), rank, world))
+
+    def commIpcExport(self):
+        self.calls.append(("ipc_export",))
+        return bytes([self.rank]) * 64
+
+    def commIpcImport(self, handles):
+        self.calls.append(("ipc_import", [h[0] for h in handles]))
+
+    def commNvlsExport(self):
+        self.calls.append(("nvls_export",))
+        return (1000 + self.rank, 50 + self.rank) if self.multicast else None
+
+    def commNvlsImport(self, pairs):
+        self.calls.append(("nvls_import", [tuple(p) for p in pairs]))
+
+    def commNvlsTeam(self, pid_fd=None):
+        self.calls.append(("nvls_team", pid_fd))
+        return (1000, 99)
+
+    def commNvlsBind(self):
+        self.calls.append(("nvls_bind",))
+
+
+def gloo_init_comm_worker(rank, world, port, out_dir):
+    """dp.init_comm's three set-ups over gloo with a recording net: what travels between the ranks and in which
+    order the library is called (the device side of the same sequence runs in test_world2_matches_single_gpu)"""
+    import pickle
+    from unittest import mock
+    import __graft_entry__ as ge
+    dist = _init(rank, world, port, "gloo")
+    g = ge.load_package()
+    out = {}
+    with mock.patch.object(g.nets, "commUniqueId", lambda: b"u" * 128):
+        for mode, multicast in [("nccl", True), ("p2p", True), ("nvls", True), ("nvls", False)]:
+            os.environ["B2NN_DP"] = mode
+            net = _RecordingNet(rank, multicast)
+            g.dp.init_comm(net, dist)
+            out[(mode, multicast)] = net.calls
+    os.environ.pop("B2NN_DP")
+    with open(os.path.join(out_dir, "calls_%d.pkl" % rank), "wb") as f:
+        pickle.dump(out, f)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def nccl_worker(rank, world, port, out_dir):
     """BF16 nets, one per GPU, stepping on their slice of each global batch with the per-layer NCCL
     all-reduce inside libb2nn.so; rank 0 also steps an un-sharded net on the whole global batch."""

@@ -43,6 +43,26 @@ def test_gloo_world2_sharded_gradient_sum_equals_single_process(g, orc, tmp_path
     assert np.abs(w_dp - net.get_weights()).max() < 1e-14
 
 
+def test_gloo_world2_init_comm_sequences(g, tmp_path):
+    """the three exchange set-ups of dp.init_comm: rank 0's NCCL id reaches everyone; p2p all-gathers the IPC
+    handles in rank order; nvls all-gathers (pid, fd), rank 0 creates the multicast object and the others get ITS
+    (pid, fd); without multicast support nvls falls back to p2p on every rank"""
+    import pickle
+    import torch.multiprocessing as mp
+    from tests import dp_workers
+    mp.spawn(dp_workers.gloo_init_comm_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    calls = [pickle.load(open(tmp_path / ("calls_%d.pkl" % r), "rb")) for r in range(2)]
+    for r in range(2):
+        c = calls[r]
+        assert c[("nccl", True)] == [("init", b"u" * 128, r, 2)]
+        assert c[("p2p", True)][1:] == [("ipc_export",), ("ipc_import", [0, 1])]
+        pairs = [(1000, 50), (1001, 51)]
+        team_arg = None if r == 0 else (1000, 99)
+        assert c[("nvls", True)][1:] == [("nvls_export",), ("nvls_import", pairs), ("nvls_team", team_arg),
+                                         ("nvls_bind",)]
+        assert c[("nvls", False)][1:] == [("nvls_export",), ("ipc_export",), ("ipc_import", [0, 1])]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["p2p", "nccl", "nvls"])
 def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
