@@ -59,7 +59,11 @@ struct JavaRandom {
     }
 };
 
-inline int pad8(int x) { return (x + 7) & ~7; }
+// leading dimension of a row-major BF16 / FP32 array with x columns: rows of wide arrays start on 128-byte
+// boundaries (64 BF16) so that every 128-byte TMA box row is ONE L2 line -- with a 1000-wide layer padded only to 8
+// the 2000-byte pitch made each box row straddle two lines (measured: the MMA warp of the K=1000 delta GEMM waited
+// for operands 48 % of its time); small arrays keep the 16-byte granularity TMA requires
+inline int pad8(int x) { return x >= 64 ? (x + 63) & ~63 : (x + 7) & ~7; }
 constexpr size_t DP_FLAG_BYTES = 8192;  // head of the arena: cross-GPU flags of the fused reduce/update kernel
 constexpr int DP_MAX_WORLD = 8;
 

@@ -71,6 +71,7 @@ struct GemmArgs {
     int act;
     float act_param;
     unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
+    unsigned int *stalls;        // debug (B2NN_GEMM_STALLS=1): [cta][8] cycle counters of the role warps, or null
 };
 
 __device__ __forceinline__ float act_apply(int act, float p, float z) {
@@ -350,6 +351,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            uint32_t st_wait = 0;
             for (int item = ring.next(false, 0); item < sched.total; item = ring.next(false, 0)) {
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
@@ -358,7 +360,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 const int bn0 = n0 + rank * (bn / 2);       // this CTA's rows of B
                 const uint32_t tx = 2u * (uint32_t)(GEMM_A_BYTES + b_chunks * GEMM_CHUNK_BYTES);
                 for (int kb = 0; kb < k_blocks; kb++) {
+                    const uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (g.stalls) st_wait += (uint32_t)clock64() - c0;
                     if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], tx);
                     uint8_t *sa = smem_a + stage * GEMM_A_BYTES, *sb = smem_b + stage * GEMM_B_BYTES;
                     const int k0 = kb * GEMM_BK;
@@ -374,6 +378,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (g.stalls) g.stalls[blockIdx.x * 8 + 0] = st_wait;
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
@@ -382,17 +387,23 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
+            uint32_t st_full = 0, st_tempty = 0, st_items = 0;
+            const uint32_t st_begin = (uint32_t)clock64();
             // bytes to step 16 along K inside a staged tile: 32 B in a K-major row, 16 rows of 128 B otherwise
             constexpr uint64_t a_kstep = (A_MN ? 2048 : 32) >> 4, b_kstep = (B_MN ? 2048 : 32) >> 4;
             for (int item = ring.next(false, 0); item < sched.total; item = ring.next(false, 0)) {
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
                 const uint32_t idesc = ptx::make_idesc_bf16(2 * GEMM_BM, bn, A_MN, B_MN);
+                uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
                 ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // both CTAs' epilogues drained this accumulator
+                if (g.stalls) { st_tempty += (uint32_t)clock64() - c0; st_items++; }
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)acc * GEMM_BN;
                 for (int kb = 0; kb < k_blocks; kb++) {
+                    c0 = g.stalls ? (uint32_t)clock64() : 0u;
                     ptx::mbar_wait(&full_bar[stage], phase);
+                    if (g.stalls) st_full += (uint32_t)clock64() - c0;
                     ptx::tc_fence_after();
                     const uint32_t sa = ptx::smem_u32(smem_a + stage * GEMM_A_BYTES);
                     const uint32_t sb = ptx::smem_u32(smem_b + stage * GEMM_B_BYTES);
@@ -408,6 +419,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 }
                 ptx::mma_commit_pair(&tfull_bar[acc]);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (g.stalls) {
+                unsigned int *o = g.stalls + blockIdx.x * 8;
+                o[1] = st_full; o[2] = st_tempty; o[3] = (uint32_t)clock64() - st_begin; o[4] = st_items;
             }
         } else if (rank == 1 && lane == 0 && g.tile_counter != nullptr) {
             // ===================== scheduler of the pair (the peer's idle MMA warp) =====================
@@ -441,10 +456,13 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int part = (warp - 2) >> 2;       // which half of the tile's columns
         int acc = 0;
         uint32_t acc_phase = 0;
+        uint32_t st_tfull = 0, st_busy = 0;
         for (int item = ring.next(true, lane); item < sched.total; item = ring.next(true, lane)) {
             int m0, n0, bn;
             sched.decode(item, m0, n0, bn);
+            const uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+            const uint32_t c1 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::tc_fence_after();
             const int m = m0 + rank * GEMM_BM + q * 32 + lane;
             const int cbeg = part * (bn / 2), cend = cbeg + bn / 2;
@@ -459,8 +477,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive_leader(&tempty_bar[acc]);
+            if (g.stalls) { st_tfull += c1 - c0; st_busy += (uint32_t)clock64() - c1; }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (g.stalls && warp == 2 && lane == 0) { g.stalls[blockIdx.x * 8 + 5] = st_tfull; g.stalls[blockIdx.x * 8 + 6] = st_busy; }
     }
 
     ptx::tc_fence_before();

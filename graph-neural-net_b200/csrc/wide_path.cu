@@ -113,7 +113,29 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
     GemmArgs ga = g;
     ga.tile_counter = net->dynamic_tiles ? net->tile_counter : nullptr;
+    static const bool want_stalls = getenv("B2NN_GEMM_STALLS") != nullptr;  // debug: where the role warps wait
+    static unsigned int *stalls_dev = nullptr;
+    if (want_stalls) {
+        if (!stalls_dev) B2_CHECK_CUDA(cudaMalloc(&stalls_dev, 8 * 148 * 2 * sizeof(unsigned int)));
+        B2_CHECK_CUDA(cudaMemsetAsync(stalls_dev, 0, 8 * 148 * 2 * sizeof(unsigned int), net->stream));
+        ga.stalls = stalls_dev;
+    }
     gemm_bf16_pair_kernel<EPI, A_MN, B_MN><<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
+    if (want_stalls) {
+        static int printed = 0;
+        std::vector<unsigned int> h(8 * 2 * pairs);
+        B2_CHECK_CUDA(cudaMemcpyAsync(h.data(), stalls_dev, h.size() * sizeof(unsigned int), cudaMemcpyDeviceToHost, net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        double s[8] = {0};
+        for (int c = 0; c < 2 * pairs; c++)
+            for (int k = 0; k < 8; k++) s[k] += h[8 * c + k];
+        const double P = pairs, C = 2.0 * pairs;
+        if (printed++ < 64)
+            fprintf(stderr, "[stalls] epi %d M %d N %d K %d: per leader: total %.0f clk, items %.2f, wait full %.0f, wait tempty %.0f | "
+                            "producer wait empty %.0f | epilogue warp 2: wait tfull %.0f, busy %.0f (per item %.0f)\n",
+                    EPI, g.M, g.N, g.K, s[3] / P, s[4] / P, s[1] / P, s[2] / P, s[0] / C, s[5] / C, s[6] / C,
+                    s[6] / C / (s[4] / P));
+    }
     if (net->profiling) {
         B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
         net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
