@@ -85,6 +85,56 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
     const int lab = labels ? labels[b] : -1;
     __nv_bfloat16 *drow = d + (size_t)b * ld_d;
     float mx = 0.f, inv = 1.f, lse = 0.f;
+    if (kind == 0 && t == nullptr && dL <= 1024 && ((ld_z | ld_d) & 3) == 0) {
+        // softmax / cross-entropy with labels, row held in registers: ONE pass over global memory, 16-byte loads
+        // and 8-byte stores, all of a lane's loads in flight together (the three-pass loop below was latency-bound:
+        // 16 us for 4096 x 1000 against 4 us of HBM time)
+        float4 x[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int c = 128 * i + 4 * lane;
+            x[i] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+            if (c + 4 <= dL) x[i] = *reinterpret_cast<const float4 *>(z + c);
+            else if (c < dL) {
+                x[i].x = z[c];
+                if (c + 1 < dL) x[i].y = z[c + 1];
+                if (c + 2 < dL) x[i].z = z[c + 2];
+            }
+        }
+        mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 8; i++) mx = fmaxf(mx, fmaxf(fmaxf(x[i].x, x[i].y), fmaxf(x[i].z, x[i].w)));
+        mx = warp_max(mx);
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {  // exp(-inf) = 0 for the masked columns
+            x[i].x = __expf(x[i].x - mx); x[i].y = __expf(x[i].y - mx);
+            x[i].z = __expf(x[i].z - mx); x[i].w = __expf(x[i].w - mx);
+            sum += (x[i].x + x[i].y) + (x[i].z + x[i].w);
+        }
+        sum = warp_sum(sum);
+        inv = 1.f / sum;
+        lse = __logf(sum);
+        if (lab >= 0 && lab < dL && (lab >> 2 & 31) == lane) lacc = lse - (z[lab] - mx);  // -log p[label]
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int c = 128 * i + 4 * lane;
+            if (c >= dL) continue;
+            float p0 = x[i].x * inv, p1 = x[i].y * inv, p2 = x[i].z * inv, p3 = x[i].w * inv;
+            if (lab == c) p0 -= 1.f;
+            if (lab == c + 1) p1 -= 1.f;
+            if (lab == c + 2) p2 -= 1.f;
+            if (lab == c + 3) p3 -= 1.f;
+            if (c + 4 <= dL) *reinterpret_cast<uint2 *>(drow + c) = make_uint2(pack_bf16x2(p0, p1), pack_bf16x2(p2, p3));
+            else {
+                drow[c] = __float2bfloat16_rn(p0);
+                if (c + 1 < dL) drow[c + 1] = __float2bfloat16_rn(p1);
+                if (c + 2 < dL) drow[c + 2] = __float2bfloat16_rn(p2);
+            }
+        }
+        lacc = warp_sum(lacc);
+        if (lane == 0 && row_loss) row_loss[b] = lacc;
+    } else {
     if (kind == 0) {
         mx = -INFINITY;
         for (int c = lane; c < dL; c += 32) mx = fmaxf(mx, z[c]);
@@ -121,6 +171,7 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
     }
     lacc = warp_sum(lacc);
     if (lane == 0 && row_loss) row_loss[b] = lacc;
+    }
     }
     // optional batch loss sum with a fixed summation order (rows within a block, then blocks in index order by
     // whichever block finishes last), so a run is reproducible bit for bit and needs no extra launch
