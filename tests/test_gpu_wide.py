@@ -151,6 +151,27 @@ def test_dense_target_step_matches_labeled(g):
     assert np.array_equal(a.getWeights(), b.getWeights())
 
 
+def test_host_pinned_bf16_rows_match_device(g):
+    """rows staged on the host as BF16 bit patterns (what bench.py's e2e leg feeds) against the same values resident
+    on the device as FP32; inputs of both signs so that the input activation f(x) (S:183-186) is exercised"""
+    dims, B = [256, 128, 32], 64
+    a, b = wide_net(g, dims), wide_net(g, dims)
+    rng = np.random.RandomState(5)
+    x = (rng.rand(512, 256).astype(np.float32) - 0.5)
+    u = x.view(np.uint32)
+    bits = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)          # round to nearest even
+    x_rounded = (bits.astype(np.uint32) << 16).view(np.float32)
+    lab = rng.randint(0, 32, 512).astype(np.int32)
+    da = g.Dataset(a, x_rounded, labels=lab, location=g.capi.DATA_DEVICE)
+    db = g.Dataset(b, bits, labels=lab, location=g.capi.DATA_HOST_PINNED)
+    idx = g.Sampler(512, seed=1).draw(6, B)
+    import ctypes as C
+    for net, ds in ((a, da), (b, db)):
+        g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), 6, B,
+                                                     0.05, 0.9, None))
+    assert np.array_equal(a.getWeights(), b.getWeights())
+
+
 def test_loss_curve_and_eval(g, orc):
     dims, B, n, iters = [256, 192, 128, 16], 128, 2048, 40
     net = wide_net(g, dims)
