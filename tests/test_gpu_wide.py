@@ -137,6 +137,39 @@ def test_one_step_vs_bf16_model_and_oracle(g, orc, dims, B):
         off += n
 
 
+@pytest.mark.parametrize("inner", ["sigmoid", "tanh", "relu"])
+def test_general_net_smooth_activations_vs_oracle(g, orc, inner):
+    """GeneralNeuralNet semantics (G:183-221, G:251-307, G:317-366) on the tensor-core path: `inner` activation in the
+    hidden layers AND on the input (Q2), sigmoid output, half squared error with dense targets.  Smooth activations
+    have no slope flips, so three momentum steps stay within 3e-2 (Frobenius, per layer) of the FP64 oracle and the
+    batch loss within 2e-2; ReLU flips like leaky-ReLU: 1e-1 and cosine >= 0.99."""
+    dims, B = [320, 256, 192, 24], 128
+    acts = {"sigmoid": (g.SIGMOID, g.SIGMOID_PRIME), "tanh": (g.TANH, g.TANH_PRIME), "relu": (g.RELU, g.RELU_PRIME)}
+    f, fp = acts[inner]
+    net = g.GeneralNeuralNet(dims, f, fp, g.SIGMOID, g.SIGMOID_PRIME, g.HALF_SQUARED_ERROR,
+                             g.HALF_SQUARED_ERROR_PRIME, precision=g.capi.PREC_BF16, flags=g.capi.FLAG_SCALED_INIT)
+    ref = orc.OracleNet(dims, kind=orc.NET_GENERAL, inner_act=inner, inner_param=0.0, last_act="sigmoid")
+    ref.set_weights(net.getWeights())
+    rng = np.random.RandomState(3)
+    x = bf16_round(rng.rand(B, dims[0]) - 0.3)          # exactly representable inputs of both signs
+    t = rng.rand(B, dims[-1])
+    w0 = ref.get_weights()
+    for it in range(3):
+        ref_loss = sum(ref.loss(x[i], t[i]) for i in range(B)) / B
+        loss = net.gradientStep((x, t), 0.5, 0.9, returnLoss=True)
+        ref.gradient_step(x, t, 0.5, 0.9)
+        assert abs(loss - ref_loss) <= 2e-2 * max(1.0, abs(ref_loss)), (it, loss, ref_loss)
+    du, du_ref = w0 - net.getWeights(), w0 - ref.get_weights()
+    tol, cos_min = (1e-1, 0.99) if inner == "relu" else (3e-2, 0.999)
+    off = 0
+    for l in range(len(dims) - 1):
+        n = dims[l] * dims[l + 1]
+        a, r = du[off:off + n], du_ref[off:off + n]
+        assert np.linalg.norm(a - r) <= tol * np.linalg.norm(r), (l, np.linalg.norm(a - r) / np.linalg.norm(r))
+        assert a @ r >= cos_min * np.linalg.norm(a) * np.linalg.norm(r)
+        off += n
+
+
 def test_dense_target_step_matches_labeled(g):
     dims, B = [256, 128, 32], 64
     a, b = wide_net(g, dims), wide_net(g, dims)
