@@ -211,14 +211,25 @@ def run_b2nn(args):
     sampler_thread = ClockSampler(local_rank)
     sampler_thread.start()
 
-    if bf16:
-        net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
-                                             flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX,
-                                             device=local_rank)
-    else:
-        net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
+    def make_net():
+        if bf16:
+            return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+                                                  flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX,
+                                                  device=local_rank)
+        return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
+
+    net = make_net()
     if world > 1:
-        g.dp.init_comm(net, dist, rank, world)
+        try:
+            g.dp.init_comm(net, dist, rank, world)
+        except RuntimeError as e:
+            # the in-switch exchange could not be set up (raised on every rank alike, dp._agree): its arena has
+            # already moved, so start over with plain peer memory
+            sys.stderr.write("[bench] %s -- falling back to B2NN_DP=p2p\n" % e)
+            net.close()
+            os.environ["B2NN_DP"] = "p2p"
+            net = make_net()
+            g.dp.init_comm(net, dist, rank, world)
     stream = torch.cuda.current_stream()
     net.setStream(stream.cuda_stream)
 

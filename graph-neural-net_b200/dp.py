@@ -60,9 +60,21 @@ def init_comm(net, dist, rank=None, world=None):
     return rank, world
 
 
+def _agree(dist, world, ok, what):
+    """every rank learns whether `what` succeeded everywhere, so that all ranks take the same branch (a rank that
+    raised alone would leave the others waiting in the next collective)"""
+    flags = [None] * world
+    dist.all_gather_object(flags, None if ok is True else str(ok))
+    bad = [(r, f) for r, f in enumerate(flags) if f is not None]
+    if bad:
+        raise RuntimeError("NVSwitch multicast set-up failed in %s on rank(s) %s: %s (set B2NN_DP=p2p to use plain "
+                           "peer memory)" % (what, [r for r, _ in bad], bad[0][1]))
+
+
 def _init_nvls(net, dist, rank, world):
     """NVSwitch multicast set-up (include/b2nn.h, b2nn_comm_nvls_*): only (pid, fd) pairs travel through
-    the process group.  False (on every rank) when any rank lacks multicast support."""
+    the process group.  False (on every rank) when any rank lacks multicast support; RuntimeError on EVERY rank
+    when a later stage fails anywhere (the arena has moved by then: re-create the net to fall back)."""
     mine = net.commNvlsExport()
     pairs = [None] * world
     dist.all_gather_object(pairs, mine)
@@ -70,12 +82,18 @@ def _init_nvls(net, dist, rank, world):
         if mine is not None:
             raise RuntimeError("multicast support differs between ranks")
         return False
-    net.commNvlsImport(pairs)
-    team = [net.commNvlsTeam(None) if rank == 0 else None]
+
+    def stage(what, fn):
+        try:
+            out, ok = fn(), True
+        except Exception as e:  # noqa: BLE001 -- reported on all ranks by _agree
+            out, ok = None, "%s: %s" % (type(e).__name__, e)
+        _agree(dist, world, ok, what)
+        return out
+
+    stage("import of the peers' arenas", lambda: net.commNvlsImport(pairs))
+    team = [stage("creation of the multicast object", lambda: net.commNvlsTeam(None) if rank == 0 else None)]
     dist.broadcast_object_list(team, src=0)   # rank 0 keeps its fd open until everybody has duplicated it
-    if rank != 0:
-        net.commNvlsTeam(team[0])
-    dist.barrier()                            # every device joined the team
-    net.commNvlsBind()
-    dist.barrier()
+    stage("joining the multicast team", lambda: net.commNvlsTeam(team[0]) if rank != 0 else None)
+    stage("binding the arena", lambda: net.commNvlsBind())   # _agree doubles as the barrier before / after the bind
     return True

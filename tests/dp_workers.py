@@ -105,6 +105,18 @@ def gloo_init_comm_worker(rank, world, port, out_dir):
             net = _RecordingNet(rank, multicast)
             g.dp.init_comm(net, dist)
             out[(mode, multicast)] = net.calls
+        # a stage failing on ONE rank must raise on EVERY rank (nobody is left waiting in a collective)
+        os.environ["B2NN_DP"] = "nvls"
+        net = _RecordingNet(rank, True)
+        if rank == 1:
+            def boom(pairs):
+                raise ValueError("cuMemImportFromShareableHandle -> 999")
+            net.commNvlsImport = boom
+        try:
+            g.dp.init_comm(net, dist)
+            out["failure"] = "no exception"
+        except RuntimeError as e:
+            out["failure"] = str(e)
     os.environ.pop("B2NN_DP")
     with open(os.path.join(out_dir, "calls_%d.pkl" % rank), "wb") as f:
         pickle.dump(out, f)
