@@ -314,8 +314,12 @@ def run_b2nn(args):
     if bf16:
         # host rows in the operand precision of this mode (BF16 bits, rounded to nearest even once at staging time,
         # like the reference's one-off (byte & 0xff) / 255.0 at load, MNISTTrainer.java:97)
-        u = x.view(np.uint32)
-        x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+        if args.e2e_rows == "u8":
+            # rows in the reference's own storage format, IDX pixel bytes read as (raw & 0xff) / 255.0 (M:97)
+            x_host = np.minimum(np.floor(x * 256.0), 255.0).astype(np.uint8)
+        else:
+            u = x.view(np.uint32)
+            x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
         x_host_bytes = B * dims[0] * x_host.dtype.itemsize
         ds_e2e = g.Dataset(net, x_host, labels=labels, location=g.capi.DATA_HOST_PINNED)
     else:
@@ -333,7 +337,8 @@ def run_b2nn(args):
     e2e = {"value": world * B * K / e2e_s, "unit": "samples/s",
            "h2d_bytes_per_step": (x_host_bytes if bf16 else 0) + B * 4, "d2h_bytes_per_step": 8,
            "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]),
-           "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset of BF16 rows: every step's batch rows are "
+           "rows": args.e2e_rows if bf16 else "f64",
+           "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset of BF16 (or, with --e2e-rows u8, pixel-byte) rows: every step's batch rows are "
                     "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
                     "(double-buffered under the previous step's GEMMs); per-step loss read back" if bf16 else
                     "b2nn_train_indexed over the device-resident dataMaster (784-wide rows live on the GPU like "
@@ -416,6 +421,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b2nn", choices=["b2nn", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--e2e-rows", default="bf16", choices=["bf16", "u8"],
+                    help="element type of the pinned host rows of the e2e leg (u8 = IDX pixel bytes / 255)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the 784-300-100-10 side measurement")
     args = ap.parse_args()

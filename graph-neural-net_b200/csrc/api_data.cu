@@ -14,7 +14,7 @@ using namespace b2nn;
 
 namespace {
 
-size_t dtype_size(int dt) { return dt == B2NN_DT_F64 ? 8 : dt == B2NN_DT_F32 ? 4 : 2; }
+size_t dtype_size(int dt) { return dt == B2NN_DT_F64 ? 8 : dt == B2NN_DT_F32 ? 4 : dt == B2NN_DT_BF16 ? 2 : 1; }
 
 int check_pair(b2nn_net *net, b2nn_dataset *ds) {
     B2_REQUIRE(net != nullptr && ds != nullptr, B2NN_ERR_INVALID_ARG, "null handle");
@@ -150,7 +150,7 @@ int b2nn_dataset_create(b2nn_net *net, const void *x, int32_t x_dtype, const dou
     *out = nullptr;
     B2_REQUIRE(net != nullptr && x != nullptr && n > 0, B2NN_ERR_INVALID_ARG, "null net/x or n <= 0");
     B2_REQUIRE((t != nullptr) != (labels != nullptr), B2NN_ERR_INVALID_ARG, "give exactly one of t / labels");
-    B2_REQUIRE(x_dtype >= B2NN_DT_F64 && x_dtype <= B2NN_DT_BF16, B2NN_ERR_INVALID_ARG, "unknown dtype %d", x_dtype);
+    B2_REQUIRE(x_dtype >= B2NN_DT_F64 && x_dtype <= B2NN_DT_U8, B2NN_ERR_INVALID_ARG, "unknown dtype %d", x_dtype);
     B2_REQUIRE(location == B2NN_DATA_DEVICE || location == B2NN_DATA_HOST_PINNED, B2NN_ERR_INVALID_ARG,
                "unknown location %d", location);
     B2_CHECK_CUDA(cudaSetDevice(net->device));

@@ -22,6 +22,58 @@ __device__ __forceinline__ float load_as_float<float>(const float *p) { return *
 template <>
 __device__ __forceinline__ float load_as_float<__nv_bfloat16>(const __nv_bfloat16 *p) { return __bfloat162float(*p); }
 
+// IDX pixel bytes: value = (raw & 0xff) / 255.0 (MNISTTrainer.java:97); the IEEE float quotient equals the double
+// quotient rounded to float for all 256 bytes (checked in tests/test_capi_cpu.py)
+template <>
+__device__ __forceinline__ float load_as_float<uint8_t>(const uint8_t *p) { return __fdiv_rn((float)*p, 255.0f); }
+
+// eight consecutive elements with the widest aligned load (one request per thread instead of eight: when X is
+// pinned host memory every request is a multi-microsecond PCIe read that occupies the SM's load path)
+template <typename T>
+__device__ __forceinline__ void load8_as_float(const T *x, float (&v)[8]) {
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = load_as_float<T>(x + e);
+}
+template <>
+__device__ __forceinline__ void load8_as_float<__nv_bfloat16>(const __nv_bfloat16 *x, float (&v)[8]) {
+    if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4 *>(x));
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const float2 f = __bfloat1622float2(h[e]);
+            v[2 * e] = f.x; v[2 * e + 1] = f.y;
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = __bfloat162float(x[e]);
+    }
+}
+template <>
+__device__ __forceinline__ void load8_as_float<float>(const float *x, float (&v)[8]) {
+    if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+        const float4 a = __ldg(reinterpret_cast<const float4 *>(x)), b = __ldg(reinterpret_cast<const float4 *>(x) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = x[e];
+    }
+}
+template <>
+__device__ __forceinline__ void load8_as_float<uint8_t>(const uint8_t *x, float (&v)[8]) {
+    if ((reinterpret_cast<uintptr_t>(x) & 7) == 0) {
+        const uint2 u = __ldg(reinterpret_cast<const uint2 *>(x));
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            v[e] = __fdiv_rn((float)((u.x >> (8 * e)) & 0xffu), 255.0f);
+            v[4 + e] = __fdiv_rn((float)((u.y >> (8 * e)) & 0xffu), 255.0f);
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = load_as_float<uint8_t>(x + e);
+    }
+}
+
 // a0 = f(x) (the reference activates the INPUT layer too, SoftmaxCrossEntropyNeuralNet.java:183-186)
 // for the rows named by idx (or rows 0..B-1), cast to BF16, stored [B][ld_a].
 // X may live in HBM or in mapped pinned host memory (then this kernel IS the host->device copy).
@@ -40,8 +92,9 @@ input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, 
         __nv_bfloat16 *o = a + (size_t)b * ld_a + i0;
         if (i0 + 8 <= d0) {
             float v[8];
+            load8_as_float<T>(x, v);
 #pragma unroll
-            for (int e = 0; e < 8; e++) v[e] = act_apply(act, act_param, load_as_float<T>(x + e));
+            for (int e = 0; e < 8; e++) v[e] = act_apply(act, act_param, v[e]);
             uint4 u;
             u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
             u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
@@ -49,6 +102,36 @@ input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, 
         } else {
             for (int e = 0; i0 + e < d0; e++) o[e] = __float2bfloat16_rn(act_apply(act, act_param, load_as_float<T>(x + e)));
         }
+    }
+}
+
+// Pixel-byte rows with d0 % 16 == 0: 16 bytes per thread per request.  Out of pinned host memory the gather is bound
+// by the round trips each thread makes one after the other, not by bytes, so twice the elements per request halve its
+// duration (and the time it spends beside the GEMMs).
+__global__ void __launch_bounds__(256)
+input_prologue_u8x16(const uint8_t *__restrict__ X, const int32_t *__restrict__ idx, int B, int d0, int act,
+                     float act_param, __nv_bfloat16 *__restrict__ a, int ld_a) {
+    const int groups = d0 >> 4;
+    const long long total = (long long)B * groups;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(t / groups), i0 = (int)(t % groups) * 16;
+        const long long src = idx ? idx[b] : b;
+        const uint4 raw = __ldg(reinterpret_cast<const uint4 *>(X + src * d0 + i0));
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        uint32_t o[8];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+                v[e] = act_apply(act, act_param, __fdiv_rn((float)((w[q] >> (8 * e)) & 0xffu), 255.0f));
+            o[2 * q] = pack_bf16x2(v[0], v[1]);
+            o[2 * q + 1] = pack_bf16x2(v[2], v[3]);
+        }
+        uint4 *dst = reinterpret_cast<uint4 *>(a + (size_t)b * ld_a + i0);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
 }
 

@@ -217,6 +217,8 @@ static int prefer_max_shared_carveout() {
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<float>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<__nv_bfloat16>,
                                        cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<uint8_t>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue_u8x16, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::output_delta, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::reduce_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_labels, cudaFuncAttributePreferredSharedMemoryCarveout, c));
@@ -408,6 +410,15 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     case B2NN_DT_BF16:
         wide::input_prologue<__nv_bfloat16><<<grid, thr, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
                                                                  net->inner_act, p, b.a[0], pad8(d0));
+        break;
+    case B2NN_DT_U8:
+        if (d0 % 16 == 0) {
+            wide::input_prologue_u8x16<<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, net->inner_act, p,
+                                                             b.a[0], pad8(d0));
+            break;
+        }
+        wide::input_prologue<uint8_t><<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
+                                                           pad8(d0));
         break;
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
     }

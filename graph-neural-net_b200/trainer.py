@@ -46,8 +46,10 @@ class Dataset:
             dt = capi.DT_F32
         elif x.dtype == np.uint16:
             dt = capi.DT_BF16
+        elif x.dtype == np.uint8:
+            dt = capi.DT_U8        # IDX pixel bytes, read as (raw & 0xff) / 255.0 (M:97)
         else:
-            raise ValueError("x must be float64, float32 or uint16 (bfloat16 bits)")
+            raise ValueError("x must be float64, float32, uint16 (bfloat16 bits) or uint8 (pixel bytes)")
         if x.ndim != 2 or x.shape[1] != net.layerDims[0]:
             raise ValueError("data rows must have the net's input dimension (T:32)")
         tp = lp = None

@@ -91,7 +91,10 @@ enum b2nn_flags {
     B2NN_FLAG_STABLE_SOFTMAX = 2
 };
 
-enum b2nn_dtype { B2NN_DT_F64 = 0, B2NN_DT_F32 = 1, B2NN_DT_BF16 = 2 };
+/* element type of dataset rows handed to b2nn_dataset_create.  B2NN_DT_U8 rows are IDX pixel bytes, read as
+ * (raw & 0xff) / 255.0 exactly like the reference's loader (MNISTTrainer.java:97); BF16 nets only (FP64 nets take
+ * the doubles and find the bytes themselves). */
+enum b2nn_dtype { B2NN_DT_F64 = 0, B2NN_DT_F32 = 1, B2NN_DT_BF16 = 2, B2NN_DT_U8 = 3 };
 
 enum b2nn_data_location {
     B2NN_DATA_DEVICE = 0,     /* rows resident in HBM */

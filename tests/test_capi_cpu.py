@@ -108,3 +108,12 @@ def test_log_row_and_idx_readers_match_oracle(g, orc, golden_dir, tmp_path):
     assert open(ip, "rb").read() == open(ip2, "rb").read()   # deterministic
     oh = mnist.one_hot(np.array([3, 0, 9]))
     assert oh.shape == (3, 10) and oh[0, 3] == 1 and oh.sum() == 3
+
+
+def test_pixel_byte_quotient_float_equals_double():
+    """the wide path reads B2NN_DT_U8 rows as the IEEE float quotient byte / 255.0f; for all 256 bytes this is the
+    double quotient of the reference's loader (MNISTTrainer.java:97) rounded to float, so byte rows and converted FP32
+    rows feed the kernels identical values"""
+    b = np.arange(256)
+    assert np.array_equal((b.astype(np.float32) / np.float32(255.0)).astype(np.float32),
+                          (b.astype(np.float64) / 255.0).astype(np.float32))

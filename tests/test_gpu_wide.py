@@ -242,6 +242,27 @@ def test_eval_argmax_last_max_wins(g):
     assert hits == 40 and (pred == 15).all()                # MNISTTrainer.java:166-168
 
 
+@pytest.mark.parametrize("d0", [256, 100])   # 100: rows not 8-byte aligned, scalar load path
+def test_pixel_byte_rows_match_float_rows(g, d0):
+    """rows kept as IDX pixel bytes in pinned host memory (B2NN_DT_U8, value = (raw & 0xff) / 255.0 as in M:97) against
+    the same rows converted on the host the way the reference's loader does and staged on the device as FP32"""
+    dims, B = [d0, 128, 32], 64
+    a, b = wide_net(g, dims), wide_net(g, dims)
+    rng = np.random.RandomState(6)
+    raw = rng.randint(0, 256, (512, d0)).astype(np.uint8)
+    x = (raw.astype(np.float64) / 255.0).astype(np.float32)
+    lab = rng.randint(0, 32, 512).astype(np.int32)
+    da = g.Dataset(a, x, labels=lab, location=g.capi.DATA_DEVICE)
+    db = g.Dataset(b, raw, labels=lab, location=g.capi.DATA_HOST_PINNED)
+    idx = g.Sampler(512, seed=1).draw(6, B)
+    import ctypes as C
+    for net, ds in ((a, da), (b, db)):
+        g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), 6, B,
+                                                     0.05, 0.9, None))
+    assert np.array_equal(a.getWeights(), b.getWeights())
+    assert da.evaluate()[0] == db.evaluate()[0]
+
+
 def test_host_pinned_dataset_matches_device(g):
     dims, B = [256, 128, 32], 64
     a, b = wide_net(g, dims), wide_net(g, dims)
