@@ -354,7 +354,7 @@ def run_b2nn(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cs, cw = (3, 1) if args.workload != "c2" else (200, 20)
+        cs, cw = {"c4": (10, 1), "c5": (3, 1), "c2": (500, 20)}[args.workload]   # ~10-15 s of CPU work each
         val, dt, r = cpu_reference_run(args.workload, cs, cw)
         cpu = {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
                "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" %
