@@ -45,6 +45,7 @@ void make_layout(const b2nn_net *net, int B, int G, Layout *out) {
     p.o_lut = take(256);
     p.o_stage = take((B * d0 + 7) / 8);  // one batch of rows as bytes
     p.o_mbar = take(2);
+    p.o_prof = take(16);
     out->smem_bytes = (size_t)o * sizeof(double);
 }
 const void *fused_kernel_for(int act) {
@@ -109,8 +110,8 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     static unsigned long long *prof_dev = nullptr;
     const bool prof = getenv("B2NN_K1_PROF") != nullptr;
     if (prof) {
-        if (!prof_dev) B2_CHECK_CUDA(cudaMalloc(&prof_dev, 8 * sizeof(unsigned long long)));
-        B2_CHECK_CUDA(cudaMemsetAsync(prof_dev, 0, 8 * sizeof(unsigned long long), net->stream));
+        if (!prof_dev) B2_CHECK_CUDA(cudaMalloc(&prof_dev, 16 * sizeof(unsigned long long)));
+        B2_CHECK_CUDA(cudaMemsetAsync(prof_dev, 0, 16 * sizeof(unsigned long long), net->stream));
     }
     p.prof = prof ? prof_dev : nullptr;
     void *args[] = {(void *)&p};
@@ -118,12 +119,15 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
                                               lo.smem_bytes, net->stream));
     net->launches++;
     if (prof) {
-        unsigned long long h[8];
+        unsigned long long h[16];
         B2_CHECK_CUDA(cudaMemcpyAsync(h, prof_dev, sizeof h, cudaMemcpyDeviceToHost, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
-        const char *names[8] = {"stage", "phase1", "barrier1", "phase2", "barrier2", "phase3", "phase4", "phase5"};
+        // slots 8..14 split phase 3 (a2 load, z3, softmax/delta3, loss; slot 5 = delta2) and phase 5 (W0, W1 columns,
+        // W1 rows; slot 7 = W2)
+        const char *names[16] = {"stage", "phase1", "barrier1", "phase2", "barrier2", "p3:delta2", "phase4", "p5:W2",
+                                 "p3:a2", "p3:z3", "p3:softmax", "p3:loss", "p5:W0", "p5:W1c", "p5:W1r", "stage:wait"};
         fprintf(stderr, "[b2nn K1 prof] cycles per step (CTA 0):");
-        for (int i = 0; i < 8; i++) fprintf(stderr, " %s %.0f", names[i], (double)h[i] / iters);
+        for (int i = 0; i < 16; i++) fprintf(stderr, " %s %.0f", names[i], (double)h[i] / iters);
         fprintf(stderr, "\n");
     }
     return B2NN_OK;

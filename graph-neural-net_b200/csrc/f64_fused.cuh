@@ -44,9 +44,10 @@ struct FusedParams {
     int o_a0, o_a1, o_a2, o_d2, o_w0, o_w1c, o_w1r, o_w2, o_z1o, o_d1o, o_z3, o_d3, o_t, o_misc;
     int o_a1o, o_part;  // own activations [B][nc0max]; chunk partial sums [KS][B][4]
     int o_w2t;  // [d3][d2] transposed copy of W2 for the delta2 pass
+    int o_prof;                  // 16 cycle counters of the measurement aid
     int o_lut, o_stage, o_mbar;  // 256-entry f(byte/255) table, byte staging for one batch, mbarrier
     int bulk;                    // rows can be fetched with cp.async.bulk (16-byte aligned rows)
-    unsigned long long *prof;    // optional [8] cycle sums per phase (CTA 0), measurement aid (B2NN_K1_PROF=1)
+    unsigned long long *prof;    // optional [16] cycle sums per phase (CTA 0), measurement aid (B2NN_K1_PROF=1)
 };
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -60,6 +61,25 @@ __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned l
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(bar, 1ULL);
+        unsigned long long v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+        } while (v < target);
+    }
+    __syncthreads();
+}
+
+// the same barrier with `work()` run by the whole CTA between this CTA's arrival and the wait for the others: thread 0
+// polls, every other warp is idle there anyway
+template <class F>
+__device__ __forceinline__ void grid_barrier_overlap(unsigned long long *bar, unsigned long long target, F work) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1ULL);
+    }
+    work();
+    if (threadIdx.x == 0) {
         unsigned long long v;
         do {
             asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
@@ -145,23 +165,28 @@ __device__ __forceinline__ void blocked_dot(const double *A, const double *Wc, i
     }
 }
 
-// issue the asynchronous fetch of the batch of step `it` (rows named by idx) into `dst`
-__device__ __forceinline__ void issue_batch_fetch(const FusedParams &p, int it, void *dst, uint64_t *mbar) {
+// issue the asynchronous fetch of the batch of step `it` (rows named by idx) into `dst`; called by all lanes of ONE
+// warp, one row per lane (a single thread issuing B copies one after the other, each behind a load of idx[b], cost
+// ~4 K cycles per step on the critical path)
+__device__ __forceinline__ void issue_batch_fetch(const FusedParams &p, int it, void *dst, uint64_t *mbar, int lane) {
     const int32_t *idx = p.idx + (size_t)it * p.B;
     const uint32_t row_bytes = p.Xu8 ? (uint32_t)p.d0 : (uint32_t)p.d0 * 8u;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy accesses to dst are done
-    mbar_expect(mbar, row_bytes * (uint32_t)p.B);
-    for (int b = 0; b < p.B; b++) {
+    if (lane == 0) mbar_expect(mbar, row_bytes * (uint32_t)p.B);
+    __syncwarp();
+    for (int b = lane; b < p.B; b += 32) {
         const size_t row = (size_t)idx[b];
         const void *src = p.Xu8 ? (const void *)(p.Xu8 + row * p.d0) : (const void *)(p.X + row * p.d0);
         bulk_row_load((char *)dst + (size_t)b * row_bytes, src, row_bytes, mbar);
     }
 }
 
+// cycle sums are kept in shared memory and written out once (a read-modify-write of global memory per mark cost
+// ~700 cycles each and distorted the intervals)
 #define K1_MARK(i)                                                      \
     if (p.prof != nullptr && c == 0 && tid == 0) {                      \
         const long long now_ = clock64();                               \
-        p.prof[i] += (unsigned long long)(now_ - tprev_);               \
+        profs[i] += (unsigned long long)(now_ - tprev_);                \
         tprev_ = now_;                                                  \
     }
 
@@ -222,9 +247,12 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     }
     if (u8 && tid < 256) lut[tid] = act(IACT, p.inner_p, (double)tid / 255.0);  // MNISTTrainer.java:97 + S:185
     __syncthreads();
-    if (p.bulk && tid == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar);
+    if (p.bulk && warp == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar, lane);
 
     unsigned long long bar_target = 0;
+    unsigned long long *profs = reinterpret_cast<unsigned long long *>(sm + p.o_prof);
+    if (p.prof != nullptr && c == 0 && tid == 0)
+        for (int i = 0; i < 16; i++) profs[i] = 0ULL;
     long long tprev_ = clock64();
     for (int it = 0; it < p.iters; it++) {
         const int32_t *idx = p.idx + (size_t)it * B;
@@ -250,6 +278,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         if (p.bulk) {
             mbar_wait_parity(mbar, (uint32_t)(it & 1));
+            K1_MARK(15)  // targets + wait for the prefetched rows
             if (u8) {
                 // d0 % 16 == 0 here: 4 bytes per lane per iteration, two 16-byte stores
                 const uint32_t *st4 = reinterpret_cast<const uint32_t *>(stage);
@@ -271,8 +300,6 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         }
         __syncthreads();
-        // the byte staging buffer is free again: fetch the NEXT batch while this step computes
-        if (p.bulk && u8 && tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar);
 
         K1_MARK(0)  // batch staged
         // ---- phase 1: z1[:, own columns] = a0 . W0[:, own]; publish ----
@@ -296,7 +323,11 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(1)  // phase 1
         bar_target += G;
-        grid_barrier(p.bar, bar_target);
+        // the byte staging buffer has been free since the batch was staged: warp 1 requests the NEXT batch while
+        // thread 0 waits for the other CTAs
+        grid_barrier_overlap(p.bar, bar_target, [&] {
+            if (p.bulk && u8 && warp == 1 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar, lane);
+        });
         K1_MARK(2)  // barrier 1
 
         // ---- phase 2: owners of W1 columns: a1 = f(z1) (all of it), z2[:, own] = a1 . W1[:, own]; publish ----
@@ -352,6 +383,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         }
         __syncthreads();
+        K1_MARK(8)
         for (int e = tid; e < B * d3; e += NT) {
             const int b = e / d3, j = e - b * d3;
             const double *ar = a2 + (size_t)b * d2;
@@ -367,6 +399,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             z3[e] = (s0 + s1) + (s2 + s3);
         }
         __syncthreads();
+        K1_MARK(9)
         if (p.kind == 0) {
             // softmax (S:357-376) + cross entropy (S:213-217) + delta (S:249-251)
             if (tid < B) {
@@ -400,6 +433,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         }
         __syncthreads();
+        K1_MARK(10)
         if (p.loss_out && c == 0) {
             // per-row loss in ascending j (one thread per row), then the batch sum in ascending b: the same
             // order of additions as a single serial loop
@@ -415,12 +449,24 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 p.loss_out[it] = tot;
             }
         }
+        K1_MARK(11)
         // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
         for (int b = warp; b < B; b += NW)
-            for (int j = lane; j < d2; j += 32) {
-                double s = 0.0;
-                for (int k = 0; k < d3; k++) s = __dadd_rn(s, __dmul_rn(w2t[k * d2 + j], dl3[b * d3 + k]));
-                dl2[b * d2 + j] = __dmul_rn(s, dl2[b * d2 + j]);
+            for (int jb = lane; jb < d2; jb += 128) {  // four columns per lane: four independent addition chains
+                double s4[4] = {0.0, 0.0, 0.0, 0.0};
+                for (int k = 0; k < d3; k++) {
+                    const double dk = dl3[b * d3 + k];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const int j = jb + 32 * q;
+                        if (j < d2) s4[q] = __dadd_rn(s4[q], __dmul_rn(w2t[k * d2 + j], dk));
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int j = jb + 32 * q;
+                    if (j < d2) dl2[b * d2 + j] = __dmul_rn(s4[q], dl2[b * d2 + j]);
+                }
             }
         __syncthreads();
 
@@ -443,31 +489,46 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         K1_MARK(6)  // phase 4
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
-        for (int k = tid; k < d0; k += NT) {
-            double vprev[FUSED_CMAX], g[FUSED_CMAX];
+        // two rows k per thread in flight (their velocity loads from L2 overlap); per element the order of the
+        // additions is unchanged
+        for (int kA = tid; kA < d0; kA += 2 * NT) {
+            const int kB = kA + NT;
+            const bool hasB = kB < d0;
+            double vpA[FUSED_CMAX], vpB[FUSED_CMAX], gA[FUSED_CMAX], gB[FUSED_CMAX];
 #pragma unroll
             for (int jj = 0; jj < FUSED_CMAX; jj++) {
-                g[jj] = 0.0;
-                vprev[jj] = (jj < nc0) ? p.V0t[(size_t)(j0 + jj) * d0 + k] : 0.0;
+                gA[jj] = 0.0; gB[jj] = 0.0;
+                vpA[jj] = (jj < nc0) ? p.V0t[(size_t)(j0 + jj) * d0 + kA] : 0.0;
+                vpB[jj] = (jj < nc0 && hasB) ? p.V0t[(size_t)(j0 + jj) * d0 + kB] : 0.0;
             }
             for (int b = 0; b < B; b++) {
-                const double a = a0[(size_t)b * d0 + k];
+                const double aA = a0[(size_t)b * d0 + kA];
+                const double aB = hasB ? a0[(size_t)b * d0 + kB] : 0.0;
 #pragma unroll
-                for (int jj = 0; jj < FUSED_CMAX; jj++)
-                    g[jj] = __dadd_rn(g[jj], __dmul_rn(d1o[b * ncm + (jj < nc0 ? jj : 0)], a));
+                for (int jj = 0; jj < FUSED_CMAX; jj++) {
+                    const double dlt = d1o[b * ncm + (jj < nc0 ? jj : 0)];
+                    gA[jj] = __dadd_rn(gA[jj], __dmul_rn(dlt, aA));
+                    gB[jj] = __dadd_rn(gB[jj], __dmul_rn(dlt, aB));
+                }
             }
 #pragma unroll
             for (int jj = 0; jj < FUSED_CMAX; jj++)
                 if (jj < nc0) {
-                    const double adj = sgd_adj(p.step, g[jj], B, invB, p.momentum, vprev[jj]);
-                    w0[jj * d0 + k] = __dsub_rn(w0[jj * d0 + k], adj);
-                    p.V0t[(size_t)(j0 + jj) * d0 + k] = adj;
+                    const double adjA = sgd_adj(p.step, gA[jj], B, invB, p.momentum, vpA[jj]);
+                    w0[jj * d0 + kA] = __dsub_rn(w0[jj * d0 + kA], adjA);
+                    p.V0t[(size_t)(j0 + jj) * d0 + kA] = adjA;
+                    if (hasB) {
+                        const double adjB = sgd_adj(p.step, gB[jj], B, invB, p.momentum, vpB[jj]);
+                        w0[jj * d0 + kB] = __dsub_rn(w0[jj * d0 + kB], adjB);
+                        p.V0t[(size_t)(j0 + jj) * d0 + kB] = adjB;
+                    }
                 }
         }
+        K1_MARK(12)
         if (p.bulk && !u8) {
             // a0 is no longer needed: fetch the next batch's FP64 rows into it while W1 / W2 are updated
             __syncthreads();
-            if (tid == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar);
+            if (warp == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar, lane);
         }
         // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
         for (int kk = 0; kk < nc1; kk++)
@@ -480,17 +541,19 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 w1c[kk * d1 + j] = __dsub_rn(w1c[kk * d1 + j], adj);
                 *vp = adj;
             }
+        K1_MARK(13)
         // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
-        for (int jj = 0; jj < nc0; jj++)
-            for (int k = tid; k < d2; k += NT) {
-                double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
-                const double vprev = *vp;
-                double g = 0.0;
-                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a1o[b * ncm + jj]));
-                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
-                w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
-                *vp = adj;
-            }
+        for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
+            const int jj = e / d2, k = e - jj * d2;
+            double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
+            const double vprev = *vp;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a1o[b * ncm + jj]));
+            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+            w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
+            *vp = adj;
+        }
+        K1_MARK(14)
         // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
         for (int e = tid; e < d2 * d3; e += NT) {
             const int i = e / d3, j = e - i * d3;
@@ -507,6 +570,8 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         K1_MARK(7)  // phase 5
     }
 
+    if (p.prof != nullptr && c == 0 && tid == 0)
+        for (int i = 0; i < 16; i++) p.prof[i] = profs[i];
     // ---- write the CTA's slices back to the canonical [in][out] state ----
     for (int jj = 0; jj < nc0; jj++)
         for (int k = tid; k < d0; k += NT) {
