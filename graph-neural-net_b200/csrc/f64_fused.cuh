@@ -153,15 +153,25 @@ __device__ __forceinline__ void blocked_dot(const double *A, const double *Wc, i
 #pragma unroll
                 for (int cc = 0; cc < FUSED_CMAX; cc++) acc[r][cc] = fma(av[r], wv[cc], acc[r][cc]);
         }
+        // 16 sums over the 32 lanes with ONE butterfly: at every step a lane keeps half of its values and hands the
+        // other half to its partner, so 8 + 4 + 2 + 1 + 1 exchanges replace 16 x 5.  Each sum is formed by the same
+        // xor tree (16, 8, 4, 2, 1) as warp_sum_d, hence the same bits.
+        static_assert(FUSED_CMAX == 4, "the butterfly below reduces a 4 x 4 block");
+        const bool u16 = (lane & 16) != 0, u8 = (lane & 8) != 0, u4 = (lane & 4) != 0, u2 = (lane & 2) != 0;
+        double v8[8], v4[4], v2[2];
 #pragma unroll
-        for (int r = 0; r < 4; r++)
+        for (int j = 0; j < 8; j++) {
+            const double lo = acc[j >> 2][j & 3], hi = acc[2 + (j >> 2)][j & 3];
+            v8[j] = (u16 ? hi : lo) + __shfl_xor_sync(0xffffffffu, u16 ? lo : hi, 16);
+        }
 #pragma unroll
-            for (int cc = 0; cc < FUSED_CMAX; cc++) {
-                if (cc < nc) {  // warp-uniform
-                    const double v = warp_sum_d(acc[r][cc]);
-                    if (lane == 0 && b0 + r < B) part[((size_t)ks * B + b0 + r) * FUSED_CMAX + cc] = v;
-                }
-            }
+        for (int j = 0; j < 4; j++) v4[j] = (u8 ? v8[4 + j] : v8[j]) + __shfl_xor_sync(0xffffffffu, u8 ? v8[j] : v8[4 + j], 8);
+#pragma unroll
+        for (int j = 0; j < 2; j++) v2[j] = (u4 ? v4[2 + j] : v4[j]) + __shfl_xor_sync(0xffffffffu, u4 ? v4[j] : v4[2 + j], 4);
+        double v1 = (u2 ? v2[1] : v2[0]) + __shfl_xor_sync(0xffffffffu, u2 ? v2[0] : v2[1], 2);
+        v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+        const int r = (u16 ? 2 : 0) + (u8 ? 1 : 0), cc = (u4 ? 2 : 0) + (u2 ? 1 : 0);  // the element this lane ended up with
+        if ((lane & 1) == 0 && cc < nc && b0 + r < B) part[((size_t)ks * B + b0 + r) * FUSED_CMAX + cc] = v1;
     }
 }
 
