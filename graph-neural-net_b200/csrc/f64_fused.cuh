@@ -343,17 +343,18 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         // ---- phase 2: owners of W1 columns: a1 = f(z1) (all of it), z2[:, own] = a1 . W1[:, own]; publish ----
         if (nc1 > 0) {
             {
+                // all of a thread's loads of the published z1 are issued before the first one is used: one L2 round
+                // trip for up to 10 x 512 values instead of one per loop trip
                 const int n = B * d1;
-                int e = tid;
-                for (; e + 3 * NT < n; e += 4 * NT) {  // 4 independent L2 loads in flight per thread
-                    const double q0 = __ldcg(z1pub + e), q1 = __ldcg(z1pub + e + NT), q2 = __ldcg(z1pub + e + 2 * NT),
-                                 q3 = __ldcg(z1pub + e + 3 * NT);
-                    a1[e] = act(IACT, p.inner_p, q0);
-                    a1[e + NT] = act(IACT, p.inner_p, q1);
-                    a1[e + 2 * NT] = act(IACT, p.inner_p, q2);
-                    a1[e + 3 * NT] = act(IACT, p.inner_p, q3);
+                constexpr int ZL = 10;
+                for (int e0 = tid; e0 < n; e0 += ZL * NT) {
+                    double q[ZL];
+#pragma unroll
+                    for (int u = 0; u < ZL; u++) q[u] = (e0 + u * NT < n) ? __ldcg(z1pub + e0 + u * NT) : 0.0;
+#pragma unroll
+                    for (int u = 0; u < ZL; u++)
+                        if (e0 + u * NT < n) a1[e0 + u * NT] = act(IACT, p.inner_p, q[u]);
                 }
-                for (; e < n; e += NT) a1[e] = act(IACT, p.inner_p, __ldcg(z1pub + e));
             }
             __syncthreads();
             blocked_dot(a1, w1c, B, d1, nc1, part, warp, lane, NW);
@@ -373,23 +374,17 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
         {
             const int n = B * d2;
-            int e = tid;
-            for (; e + 3 * NT < n; e += 4 * NT) {
-                const double q0 = __ldcg(z2pub + e), q1 = __ldcg(z2pub + e + NT), q2 = __ldcg(z2pub + e + 2 * NT),
-                             q3 = __ldcg(z2pub + e + 3 * NT);
-                dl2[e] = act_prime(IACT, p.inner_p, q0);           // f'(z2), multiplied into delta2 below
-                dl2[e + NT] = act_prime(IACT, p.inner_p, q1);
-                dl2[e + 2 * NT] = act_prime(IACT, p.inner_p, q2);
-                dl2[e + 3 * NT] = act_prime(IACT, p.inner_p, q3);
-                a2[e] = act(IACT, p.inner_p, q0);
-                a2[e + NT] = act(IACT, p.inner_p, q1);
-                a2[e + 2 * NT] = act(IACT, p.inner_p, q2);
-                a2[e + 3 * NT] = act(IACT, p.inner_p, q3);
-            }
-            for (; e < n; e += NT) {
-                const double z = __ldcg(z2pub + e);
-                dl2[e] = act_prime(IACT, p.inner_p, z);
-                a2[e] = act(IACT, p.inner_p, z);
+            constexpr int ZL = 4;
+            for (int e0 = tid; e0 < n; e0 += ZL * NT) {
+                double q[ZL];
+#pragma unroll
+                for (int u = 0; u < ZL; u++) q[u] = (e0 + u * NT < n) ? __ldcg(z2pub + e0 + u * NT) : 0.0;
+#pragma unroll
+                for (int u = 0; u < ZL; u++)
+                    if (e0 + u * NT < n) {
+                        dl2[e0 + u * NT] = act_prime(IACT, p.inner_p, q[u]);  // f'(z2), multiplied into delta2 below
+                        a2[e0 + u * NT] = act(IACT, p.inner_p, q[u]);
+                    }
             }
         }
         __syncthreads();
