@@ -510,11 +510,12 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 const double aA = a0[(size_t)b * d0 + kA];
                 const double aB = hasB ? a0[(size_t)b * d0 + kB] : 0.0;
 #pragma unroll
-                for (int jj = 0; jj < FUSED_CMAX; jj++) {
-                    const double dlt = d1o[b * ncm + (jj < nc0 ? jj : 0)];
-                    gA[jj] = __dadd_rn(gA[jj], __dmul_rn(dlt, aA));
-                    gB[jj] = __dadd_rn(gB[jj], __dmul_rn(dlt, aB));
-                }
+                for (int jj = 0; jj < FUSED_CMAX; jj++)
+                    if (jj < nc0) {  // CTA-uniform: no FP64 work for columns this CTA does not own
+                        const double dlt = d1o[b * ncm + jj];
+                        gA[jj] = __dadd_rn(gA[jj], __dmul_rn(dlt, aA));
+                        gB[jj] = __dadd_rn(gB[jj], __dmul_rn(dlt, aB));
+                    }
             }
 #pragma unroll
             for (int jj = 0; jj < FUSED_CMAX; jj++)
