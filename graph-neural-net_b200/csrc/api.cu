@@ -55,7 +55,6 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     }
     B2_REQUIRE(precision == B2NN_PREC_F64 || precision == B2NN_PREC_BF16 || precision == B2NN_PREC_TF32,
                B2NN_ERR_INVALID_ARG, "unknown precision %d", precision);
-    B2_REQUIRE(precision != B2NN_PREC_TF32, B2NN_ERR_UNSUPPORTED, "TF32 path not implemented yet");
 
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -68,9 +67,9 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
     B2_CHECK_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
     B2_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
-    if (precision == B2NN_PREC_BF16)
+    if (is_wide_precision(precision))
         B2_REQUIRE(prop.major == 10, B2NN_ERR_UNSUPPORTED,
-                   "the BF16 path is tcgen05 code for sm_100a; device is sm_%d%d", prop.major, prop.minor);
+                   "the BF16 / TF32 path is tcgen05 code for sm_100a; device is sm_%d%d", prop.major, prop.minor);
 
     b2nn_net *net = new b2nn_net();
     net->device = device;

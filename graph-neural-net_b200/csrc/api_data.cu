@@ -258,7 +258,7 @@ int b2nn_train_indexed(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx, int3
                                momentum, loss_dev));
     } else {
         const char *pl = getenv("B2NN_PIPELINE");
-        if (net->precision == B2NN_PREC_BF16 && ds->labels != nullptr && iters > 1 && !(pl && pl[0] == '0')) {
+        if (is_wide_precision(net->precision) && ds->labels != nullptr && iters > 1 && !(pl && pl[0] == '0')) {
             B2_TRY(wide_train_pipelined(net, ds, idx_dev, iters, B, step, momentum, loss_dev));
         } else {
             for (int it = 0; it < iters; it++)
@@ -266,7 +266,7 @@ int b2nn_train_indexed(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx, int3
                                          loss_dev ? loss_dev + it : nullptr));
         }
     }
-    if (net->precision == B2NN_PREC_BF16) B2_TRY(wide_join(net));  // side-stream updates belong to this call
+    if (is_wide_precision(net->precision)) B2_TRY(wide_join(net));  // side-stream updates belong to this call
     if (net->trace) trace_dump(net, 3, 2);
     if (per_step_loss_or_null) {
         B2_CHECK_CUDA(cudaMemcpyAsync(per_step_loss_or_null, loss_dev, loss_bytes, cudaMemcpyDeviceToHost, net->stream));

@@ -235,8 +235,8 @@ int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, co
     B2_REQUIRE(x && labels, B2NN_ERR_INVALID_ARG, "null batch");
     B2_REQUIRE(B > 0 && step > 0, B2NN_ERR_INVALID_ARG, "batch must not be empty and step must be positive");
     B2_REQUIRE(x_dtype >= B2NN_DT_F64 && x_dtype <= B2NN_DT_BF16, B2NN_ERR_INVALID_ARG, "unknown dtype %d", x_dtype);
-    B2_REQUIRE(net->precision == B2NN_PREC_BF16, B2NN_ERR_UNSUPPORTED,
-               "labeled/narrow-dtype steps are for BF16 nets; FP64 nets take b2nn_gradient_step");
+    B2_REQUIRE(is_wide_precision(net->precision), B2NN_ERR_UNSUPPORTED,
+               "labeled/narrow-dtype steps are for BF16 / TF32 nets; FP64 nets take b2nn_gradient_step");
     B2_TRY(wide_ensure_batch(net, B));
     B2_TRY(wide_rows_from_host(net, x, x_dtype, B));
     B2_CHECK_CUDA(cudaMemcpyAsync(net->wb.labels, labels, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice,

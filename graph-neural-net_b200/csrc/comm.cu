@@ -80,7 +80,8 @@ int comm_unique_id(void *id128) {
 int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
     B2_REQUIRE(world >= 1 && rank >= 0 && rank < world, B2NN_ERR_INVALID_ARG, "bad rank/world %d/%d", rank, world);
     B2_REQUIRE(net->precision == B2NN_PREC_BF16, B2NN_ERR_UNSUPPORTED,
-               "data-parallel training is implemented for the BF16 path only (tiny FP64 nets are replicas only)");
+               "data-parallel training is implemented for the BF16 path only (tiny FP64 nets are replicas only; TF32 nets "
+               "are single-GPU: the fused exchange kernel replicates a BF16 operand copy they do not have)");
     if (world == 1) { net->rank = 0; net->world = 1; return B2NN_OK; }
     NcclApi *a = nccl();
     B2_REQUIRE(a != nullptr, B2NN_ERR_NCCL, "NCCL library not found (set B2NN_NCCL_LIB)");

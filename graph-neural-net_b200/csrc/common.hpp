@@ -64,6 +64,8 @@ struct JavaRandom {
 // the 2000-byte pitch made each box row straddle two lines (measured: the MMA warp of the K=1000 delta GEMM waited
 // for operands 48 % of its time); small arrays keep the 16-byte granularity TMA requires
 inline int pad8(int x) { return x >= 64 ? (x + 63) & ~63 : (x + 7) & ~7; }
+// the tensor-core ("wide") path serves both reduced-precision modes; TF32 nets keep FP32 operands
+inline bool is_wide_precision(int precision) { return precision == B2NN_PREC_BF16 || precision == B2NN_PREC_TF32; }
 constexpr size_t DP_FLAG_BYTES = 8192;  // head of the arena: cross-GPU flags of the fused reduce/update kernel
 constexpr int DP_MAX_WORLD = 8;
 
@@ -80,29 +82,32 @@ struct WideLayer {
     float *w = nullptr;         // FP32 master [in][ld_n]
     float *v = nullptr;         // FP32 velocity [in][ld_n]
     float *g = nullptr;         // FP32 summed gradient [in][ld_n]
-    __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]: GEMM operand copy (MN-major B forward, K-major B delta)
-    CUtensorMap tm_w;             // 64 x 64 box map over wn
+    __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]: GEMM operand copy (MN-major B forward, K-major B delta); null for TF32 nets
+    CUtensorMap tm_w;             // box map over wn (BF16 nets) or over w itself (TF32 nets), read K-major (delta GEMM)
+    CUtensorMap tm_w_mn;          // the map the forward GEMM reads it MN-major with (TF32: 32-byte-atom swizzle; BF16: == tm_w)
 };
 
 // activations / deltas for one batch size (row-major only; the GEMMs read either major-ness)
 struct WideBatch {
     int B = 0;
-    std::vector<__nv_bfloat16 *> a;    // a[l]  [B][pad8(d_l)]   l = 0..L-1 (activations incl. f(x))
-    std::vector<__nv_bfloat16 *> d;    // d[l]  [B][pad8(d_l)]   l = 1..L   (deltas)
+    // operand-typed arrays: BF16 for B2NN_PREC_BF16 nets, FP32 (read as TF32) for B2NN_PREC_TF32 nets
+    std::vector<void *> a;             // a[l]  [B][pad8(d_l)]   l = 0..L-1 (activations incl. f(x))
+    std::vector<void *> d;             // d[l]  [B][pad8(d_l)]   l = 1..L   (deltas)
     float *logits = nullptr;           // [B][pad8(d_L)] FP32
     float *row_loss = nullptr;         // [B]
     int32_t *labels = nullptr;         // [B]
     float *tdense = nullptr;           // [B][pad8(d_L)] FP32 dense targets (optional path)
     void *xstage = nullptr;            // staged raw input rows [B][d0] (any dtype, 8 B / element max)
-    std::vector<CUtensorMap> tm_a, tm_d;  // 64 x 64 box maps over a[l], d[l]
+    std::vector<CUtensorMap> tm_a, tm_d;  // box maps over a[l], d[l] for K-major reads (forward A, delta A)
+    std::vector<CUtensorMap> tm_a_mn, tm_d_mn;  // ... for MN-major reads (gradient GEMM; differ from the above for TF32 only)
     double *loss_sum = nullptr;        // device scalar(s)
     double *block_partial = nullptr;   // per-block loss partials of the output kernel
     unsigned int *block_counter = nullptr;
     // input double buffer: while step i computes from slot i&1, the prologue of step i+1 fills the other
     // slot on the copy stream.  a[0] / tm_a[0] / labels above alias the slot in use.
-    __nv_bfloat16 *a0_slot[2] = {nullptr, nullptr};
+    void *a0_slot[2] = {nullptr, nullptr};
     int32_t *labels_slot[2] = {nullptr, nullptr};
-    CUtensorMap tm_a0_slot[2];
+    CUtensorMap tm_a0_slot[2], tm_a0_slot_mn[2];
 };
 
 }  // namespace b2nn

@@ -1,7 +1,8 @@
 // gemm_tcgen05.cuh -- the wide-layer contraction of the MLP hot path on Blackwell tensor cores.
 //
-//   D[M,N] = sum_k A(m,k) * B(n,k)        A, B: BF16 in HBM exactly as the net stores them (row-major,
-//                                         no transposed copies);  accumulate FP32 in TMEM
+//   D[M,N] = sum_k A(m,k) * B(n,k)        A, B: BF16 (kind::f16) or FP32 read as TF32 (kind::tf32) in HBM exactly
+//                                         as the net stores them (row-major, no transposed copies);
+//                                         accumulate FP32 in TMEM
 //
 // One persistent, warp-specialised kernel run by CTA PAIRS (cluster of 2 = the two SMs of a TPC,
 // tcgen05.mma.cta_group::2): a pair owns a 256 x 256 output tile, each CTA stages ITS 128 rows of A and
@@ -22,6 +23,16 @@
 //   gradient  G_l = A_l^T . D_l+1      A = a[l] [B][d_l]     MN-major, B = d[l+1]          MN-major (K = batch)
 // Every buffer has ONE tensor map (64 x 64 box); the kernel picks coordinates and descriptors by major-ness.
 //
+// TF32 operands (gemm_tf32_pair_kernel, B2NN_PREC_TF32).  Everything above is laid out in BYTES, so the same
+// body serves 4-byte operands: a 128-byte swizzle row holds 32 elements instead of 64, hence 32 x 32 boxes
+// (4 KB), a 32-deep K block per stage (still 16 KB of A and 16 KB of B per CTA), K = 8 per instruction (still
+// four instructions per stage) and a 1024-byte instead of 2048-byte step along K in an MN-major tile.  One thing
+// is NOT the same: kind::tf32 reads an MN-major operand only from the 128-byte swizzle with 32-byte atoms
+// (descriptor layout type SWIZZLE_128B_BASE32B, TMA swizzle CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B), so a TF32 buffer
+// has two tensor maps, one per major-ness it is read in (wide_path.cu).  The
+// activations and deltas are then FP32 arrays and the B operand of the forward / delta GEMMs is the FP32
+// master weight array itself (no operand copy); TMA hands the tensor core the FP32 words as TF32.
+//
 // Wave quantisation: with T tiles on P pairs the last, partial wave is split into 256 x 128 half tiles when
 // that lets it finish in half a tile time (T mod P <= P/2), e.g. 4096^3: 256 tiles on 74 pairs = 3.5 waves
 // instead of 4.
@@ -34,7 +45,7 @@ namespace b2nn {
 
 constexpr int GEMM_BM = 128;        // rows of A per CTA (pair tile: 256)
 constexpr int GEMM_BN = 256;        // pair tile width
-constexpr int GEMM_BK = 64;         // 64 bf16 = 128 B = one swizzle row
+constexpr int GEMM_BK = 64;         // 64 bf16 = 128 B = one swizzle row (BF16 operands; GemmCfg<true> for TF32)
 constexpr int GEMM_STAGES = 6;
 constexpr int GEMM_EPI_WARPS = 8;   // two warps per TMEM lane quarter, each draining half the columns
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
@@ -47,10 +58,24 @@ constexpr uint32_t GEMM_TMEM_COLS = 512;  // 2 accumulators x 256 fp32 columns
 constexpr int GEMM_SCHED_SLOTS = 4;       // depth of the work-item ring between the scheduler and the role warps
 constexpr int GEMM_SCHED_READERS = 2 /*producers*/ + 1 /*MMA*/ + 2 * GEMM_EPI_WARPS;
 
+// operand-type dependent tile geometry; the byte layout of a stage is the same for both
+template <bool TF32>
+struct GemmCfg {
+    static constexpr int ESIZE = TF32 ? 4 : 2;
+    static constexpr int CH = 128 / ESIZE;          // elements per 128-byte swizzle row = edge of a TMA box = BK
+    static constexpr int BK = CH;                   // K depth of a stage
+    static constexpr int CHUNK_BYTES = CH * 128;    // one CH x CH box: 8 KB (BF16) / 4 KB (TF32)
+    static constexpr int CHUNKS_128 = 128 / CH;     // boxes per 128 operand rows: 2 / 4
+    static constexpr int UMMA_K = 32 / ESIZE;       // K per tcgen05.mma: 16 / 8 (32 bytes of a K-major row)
+    static constexpr int KSTEP_MN = UMMA_K * 128;   // bytes between K steps of an MN-major tile: 2048 / 1024
+};
+static_assert(GemmCfg<false>::BK == GEMM_BK && GemmCfg<false>::CHUNK_BYTES == GEMM_CHUNK_BYTES, "BF16 geometry");
+static_assert(GemmCfg<true>::CHUNKS_128 * GemmCfg<true>::CHUNK_BYTES == GEMM_A_BYTES, "TF32 stage bytes");
+
 enum EpiKind {
-    EPI_ACT = 0,        // a = f(acc): store BF16 out0[M][ld0]
+    EPI_ACT = 0,        // a = f(acc): store out0[M][ld0] in the operand type (BF16, or FP32 for TF32 nets)
     EPI_LOGITS = 1,     // store FP32 acc to out0[M][ld0]
-    EPI_DX = 2,         // d = acc * f'(from stored activation aux[M][ldaux]): store BF16 out0
+    EPI_DX = 2,         // d = acc * f'(from stored activation aux[M][ldaux]): store out0 in the operand type
     EPI_DW_UPDATE = 3,  // v = s*acc + mu*v; w -= v (FP32 master w,v [M][ldw]); BF16 copy of w to out0
     EPI_DW_STORE = 4    // store FP32 acc (the summed gradient) to w[M][ldw]
 };
@@ -59,9 +84,9 @@ enum ActKind { ACT_LEAKY_RELU = 0, ACT_SIGMOID = 1, ACT_RELU = 2, ACT_TANH = 3, 
 
 struct GemmArgs {
     int M, N, K;
-    void *out0;   // row-major output (bf16, or fp32 for EPI_LOGITS)
+    void *out0;   // row-major output (operand type, or fp32 for EPI_LOGITS)
     int ld0;
-    const __nv_bfloat16 *aux;  // stored activation for EPI_DX
+    const void *aux;  // stored activation for EPI_DX (operand type)
     int ldaux;
     float *w;  // master weights / gradient out
     float *v;  // velocity
@@ -72,6 +97,7 @@ struct GemmArgs {
     float act_param;
     unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
     unsigned int *stalls;        // debug (B2NN_GEMM_STALLS=1): [cta][8] cycle counters of the role warps, or null
+    int dbg;                     // debug (B2NN_GEMM_DBG): bit 0 = override the TF32 kernel's source-format fields with bits 4-6
 };
 
 __device__ __forceinline__ float act_apply(int act, float p, float z) {
@@ -133,6 +159,20 @@ __device__ __forceinline__ void store_f32_row(float *base, int ld, int N, int m,
     }
 }
 
+// Store 32 consecutive values of row m as fp32 (TF32 nets keep activations / deltas in FP32).
+__device__ __forceinline__ void store_f32_row(float *base, int ld, int N, int m, int n0, const float (&x)[32]) {
+    float *row = base + (size_t)m * ld + n0;
+    if (n0 + 32 <= N) {
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            reinterpret_cast<float4 *>(row)[q] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
+    } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            if (n0 + c < N) row[c] = x[c];
+    }
+}
+
 // x[c] = acc[c] * fprime(a[c]) for 32 columns, a unpacked from BF16 on the fly
 template <class F>
 __device__ __forceinline__ void dx32(const uint4 (&u)[4], const uint32_t (&r)[32], float (&x)[32], F fprime) {
@@ -148,7 +188,25 @@ __device__ __forceinline__ void dx32(const uint4 (&u)[4], const uint32_t (&r)[32
     }
 }
 
-template <int EPI>
+// the same for FP32 activations (TF32 nets)
+template <class F>
+__device__ __forceinline__ void dx32_f32(const float *arow, int n0, int N, const uint32_t (&r)[32], float (&x)[32], F fprime) {
+    if (n0 + 32 <= N) {
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const float4 a = reinterpret_cast<const float4 *>(arow)[q];
+            x[4 * q + 0] = __uint_as_float(r[4 * q + 0]) * fprime(a.x);
+            x[4 * q + 1] = __uint_as_float(r[4 * q + 1]) * fprime(a.y);
+            x[4 * q + 2] = __uint_as_float(r[4 * q + 2]) * fprime(a.z);
+            x[4 * q + 3] = __uint_as_float(r[4 * q + 3]) * fprime(a.w);
+        }
+    } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[c] = (n0 + c < N) ? __uint_as_float(r[c]) * fprime(arow[c]) : 0.f;
+    }
+}
+
+template <int EPI, bool TF32>
 __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0, const uint32_t (&r)[32]) {
     if (m >= g.M || n0 >= g.N) return;
     if constexpr (EPI == EPI_ACT) {
@@ -175,11 +233,23 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
             break;
         default: break;  // identity
         }
-        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+        if constexpr (TF32) store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, x);
+        else store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_LOGITS) {
         store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, r);
+    } else if constexpr (EPI == EPI_DX && TF32) {
+        const float *arow = reinterpret_cast<const float *>(g.aux) + (size_t)m * g.ldaux + n0;
+        float x[32];
+        switch (g.act) {  // one branch per 32 columns; f' from the stored activation
+        case ACT_LEAKY_RELU: { const float p = g.act_param; dx32_f32(arow, n0, g.N, r, x, [p](float a) { return a > 0.f ? 1.f : p; }); break; }
+        case ACT_RELU: dx32_f32(arow, n0, g.N, r, x, [](float a) { return a > 0.f ? 1.f : 0.f; }); break;
+        case ACT_SIGMOID: dx32_f32(arow, n0, g.N, r, x, [](float a) { return a * (1.f - a); }); break;
+        case ACT_TANH: dx32_f32(arow, n0, g.N, r, x, [](float a) { return 1.f - a * a; }); break;
+        default: dx32_f32(arow, n0, g.N, r, x, [](float) { return 1.f; });
+        }
+        store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_DX) {
-        const __nv_bfloat16 *arow = g.aux + (size_t)m * g.ldaux + n0;
+        const __nv_bfloat16 *arow = reinterpret_cast<const __nv_bfloat16 *>(g.aux) + (size_t)m * g.ldaux + n0;
         uint4 u[4];  // the 32 stored activations a = f(z), packed BF16
         if (n0 + 32 <= g.N) {
 #pragma unroll
@@ -203,6 +273,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
         }
         store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_DW_UPDATE) {
+        static_assert(!TF32, "the fused-update epilogue emits the BF16 operand copy; TF32 nets have none");
         // momentum SGD fused into the gradient GEMM (SoftmaxCrossEntropyNeuralNet.java:325-342):
         // adj = step*G/B + mu*prev ; W -= adj ; prev = adj.  G never reaches HBM.
         float *wrow = g.w + (size_t)m * g.ldw + n0;
@@ -290,10 +361,9 @@ struct SchedRing {
 //   empty[s]   one per CTA, signalled in both CTAs by the multicast tcgen05.commit
 //   tfull[a]   one per CTA, multicast commit -> each CTA's epilogue warps
 //   tempty[a]  leader only, 2 x GEMM_EPI_WARPS arrivals (the peer's warps arrive remotely)
-template <int EPI, bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const GemmArgs g) {
+template <int EPI, bool A_MN, bool B_MN, bool TF32>
+__device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUtensorMap &tmB, const GemmArgs &g) {
+    using Cfg = GemmCfg<TF32>;
     extern __shared__ uint8_t smem_raw[];
     // 128B swizzle needs 1024 B alignment of every box
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -317,7 +387,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int rank = (int)ptx::cluster_ctarank();
     const int num_pairs = gridDim.x >> 1;
     const TileSched sched(g.M, g.N, num_pairs);
-    const int k_blocks = (g.K + GEMM_BK - 1) / GEMM_BK;
+    const int k_blocks = (g.K + Cfg::BK - 1) / Cfg::BK;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
@@ -356,24 +426,24 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
                 const int am0 = m0 + rank * GEMM_BM;        // this CTA's rows of A
-                const int b_chunks = bn / 128;              // 64-row boxes of B per CTA: 2 (full) or 1 (half)
+                const int b_chunks = (bn / 2) / Cfg::CH;    // boxes of B per CTA: 128 (full tile) or 64 (half) rows
                 const int bn0 = n0 + rank * (bn / 2);       // this CTA's rows of B
-                const uint32_t tx = 2u * (uint32_t)(GEMM_A_BYTES + b_chunks * GEMM_CHUNK_BYTES);
+                const uint32_t tx = 2u * (uint32_t)(GEMM_A_BYTES + b_chunks * Cfg::CHUNK_BYTES);
                 for (int kb = 0; kb < k_blocks; kb++) {
                     const uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (g.stalls) st_wait += (uint32_t)clock64() - c0;
                     if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], tx);
                     uint8_t *sa = smem_a + stage * GEMM_A_BYTES, *sb = smem_b + stage * GEMM_B_BYTES;
-                    const int k0 = kb * GEMM_BK;
+                    const int k0 = kb * Cfg::BK;
 #pragma unroll
-                    for (int c = 0; c < 2; c++) {
-                        if (A_MN) ptx::tma_load_2d_pair(sa + c * GEMM_CHUNK_BYTES, &tmA, &full_bar[stage], am0 + 64 * c, k0);
-                        else ptx::tma_load_2d_pair(sa + c * GEMM_CHUNK_BYTES, &tmA, &full_bar[stage], k0, am0 + 64 * c);
+                    for (int c = 0; c < Cfg::CHUNKS_128; c++) {
+                        if (A_MN) ptx::tma_load_2d_pair(sa + c * Cfg::CHUNK_BYTES, &tmA, &full_bar[stage], am0 + Cfg::CH * c, k0);
+                        else ptx::tma_load_2d_pair(sa + c * Cfg::CHUNK_BYTES, &tmA, &full_bar[stage], k0, am0 + Cfg::CH * c);
                     }
                     for (int c = 0; c < b_chunks; c++) {
-                        if (B_MN) ptx::tma_load_2d_pair(sb + c * GEMM_CHUNK_BYTES, &tmB, &full_bar[stage], bn0 + 64 * c, k0);
-                        else ptx::tma_load_2d_pair(sb + c * GEMM_CHUNK_BYTES, &tmB, &full_bar[stage], k0, bn0 + 64 * c);
+                        if (B_MN) ptx::tma_load_2d_pair(sb + c * Cfg::CHUNK_BYTES, &tmB, &full_bar[stage], bn0 + Cfg::CH * c, k0);
+                        else ptx::tma_load_2d_pair(sb + c * Cfg::CHUNK_BYTES, &tmB, &full_bar[stage], k0, bn0 + Cfg::CH * c);
                     }
                     if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -389,12 +459,13 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             uint32_t acc_phase = 0;
             uint32_t st_full = 0, st_tempty = 0, st_items = 0;
             const uint32_t st_begin = (uint32_t)clock64();
-            // bytes to step 16 along K inside a staged tile: 32 B in a K-major row, 16 rows of 128 B otherwise
-            constexpr uint64_t a_kstep = (A_MN ? 2048 : 32) >> 4, b_kstep = (B_MN ? 2048 : 32) >> 4;
+            // bytes to step one instruction (K = 16 BF16 / 8 TF32) along K inside a staged tile: 32 B in a K-major
+            // row, UMMA_K rows of 128 B otherwise (descriptor address units of 16 B)
+            constexpr uint64_t a_kstep = (A_MN ? Cfg::KSTEP_MN : 32) >> 4, b_kstep = (B_MN ? Cfg::KSTEP_MN : 32) >> 4;
             for (int item = ring.next(false, 0); item < sched.total; item = ring.next(false, 0)) {
                 int m0, n0, bn;
                 sched.decode(item, m0, n0, bn);
-                const uint32_t idesc = ptx::make_idesc_bf16(2 * GEMM_BM, bn, A_MN, B_MN);
+                const uint32_t idesc = ptx::make_idesc(2 * GEMM_BM, bn, A_MN, B_MN, TF32);
                 uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
                 ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // both CTAs' epilogues drained this accumulator
                 if (g.stalls) { st_tempty += (uint32_t)clock64() - c0; st_items++; }
@@ -407,13 +478,24 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     ptx::tc_fence_after();
                     const uint32_t sa = ptx::smem_u32(smem_a + stage * GEMM_A_BYTES);
                     const uint32_t sb = ptx::smem_u32(smem_b + stage * GEMM_B_BYTES);
-                    const uint64_t da = A_MN ? ptx::make_desc_mnmajor_sw128(sa, GEMM_CHUNK_BYTES)
-                                             : ptx::make_desc_kmajor_sw128(sa);
-                    const uint64_t db = B_MN ? ptx::make_desc_mnmajor_sw128(sb, GEMM_CHUNK_BYTES)
-                                             : ptx::make_desc_kmajor_sw128(sb);
+                    // MN-major TF32 tiles are staged in the 32-byte-atom swizzle (the only MN-major layout kind::tf32 reads)
+                    const uint64_t da = !A_MN ? ptx::make_desc_kmajor_sw128(sa)
+                                        : TF32 ? ptx::make_desc_mnmajor_sw128_base32b(sa, Cfg::CHUNK_BYTES)
+                                               : ptx::make_desc_mnmajor_sw128(sa, Cfg::CHUNK_BYTES);
+                    const uint64_t db = !B_MN ? ptx::make_desc_kmajor_sw128(sb)
+                                        : TF32 ? ptx::make_desc_mnmajor_sw128_base32b(sb, Cfg::CHUNK_BYTES)
+                                               : ptx::make_desc_mnmajor_sw128(sb, Cfg::CHUNK_BYTES);
 #pragma unroll
-                    for (int k = 0; k < GEMM_BK / 16; k++)
-                        ptx::mma_f16_ss_pair(d_tmem, da + a_kstep * k, db + b_kstep * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; k++) {
+                        if constexpr (TF32) {
+                            // debug (B2NN_GEMM_DBG = 1 | fmt << 4): override the two source-format fields
+                            uint32_t id = idesc;
+                            if (g.dbg & 1) id = (idesc & ~0x1F80u) | (((uint32_t)g.dbg >> 4 & 7u) << 7) | (((uint32_t)g.dbg >> 4 & 7u) << 10);
+                            ptx::mma_tf32_ss_pair(d_tmem, da + a_kstep * k, db + b_kstep * k, id, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        else
+                            ptx::mma_f16_ss_pair(d_tmem, da + a_kstep * k, db + b_kstep * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
                     ptx::mma_commit_pair(&empty_bar[stage]);  // frees the slot in both CTAs when these MMAs retire
                     if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -472,7 +554,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 uint32_t r[32];
                 ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
                 ptx::tmem_ld_wait();
-                epilogue_chunk<EPI>(g, m, n0 + c0, r);
+                epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r);
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -489,6 +571,21 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         ptx::tc_fence_after();
         ptx::tmem_dealloc_pair(tmem_base, GEMM_TMEM_COLS);
     }
+}
+
+template <int EPI, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const GemmArgs g) {
+    gemm_pair_body<EPI, A_MN, B_MN, false>(tmA, tmB, g);
+}
+
+// the same kernel over FP32 buffers read as TF32 (tcgen05.mma kind::tf32), see the header comment
+template <int EPI, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tf32_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const GemmArgs g) {
+    gemm_pair_body<EPI, A_MN, B_MN, true>(tmA, tmB, g);
 }
 
 }  // namespace b2nn

@@ -204,6 +204,18 @@ __device__ __forceinline__ void mma_f16_ss_pair(uint32_t tmem_d, uint64_t desc_a
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// the same with FP32 words read as TF32 (K = 8 per instruction)
+__device__ __forceinline__ void mma_tf32_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // arrive (once) on the barrier at this offset in BOTH CTAs when the issued MMAs have retired
 __device__ __forceinline__ void mma_commit_pair(uint64_t *bar) {
     asm volatile(
@@ -239,11 +251,26 @@ __device__ __forceinline__ uint64_t make_desc_mnmajor_sw128(uint32_t smem_addr, 
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Instruction descriptor, kind::f16: BF16 x BF16 -> FP32; a_mn / b_mn select MN-major operands.
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n, bool a_mn = false, bool b_mn = false) {
+// MN-major operand of 4-byte (TF32) elements.  The tensor core reads those only from the "128B swizzle with 32-byte
+// atoms" layout (descriptor layout type 1; a plain SWIZZLE_128B descriptor makes kind::tf32 return zeros for an
+// MN-major operand -- measured): rows of 128 B (= 32 MN elements) whose four 32-byte pieces are XOR-ed with the row
+// index mod 4, written by TMA with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.  Canonical form ((8,n),(4,k)):((1,LBO),(8,SBO))
+// in 16 B units: 4-row groups 512 B apart along K (SBO), successive 32-element MN chunks `chunk_bytes` apart (LBO).
+__device__ __forceinline__ uint64_t make_desc_mnmajor_sw128_base32b(uint32_t smem_addr, uint32_t chunk_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((chunk_bytes >> 4) & 0x3FFF) << 16;  // leading byte offset: next 32 MN elements
+    d |= (uint64_t)(512 >> 4) << 32;                     // stride byte offset: next 4 K rows
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;                              // SWIZZLE_128B_BASE32B
+    return d;
+}
+// Instruction descriptor, kind::f16 (BF16 x BF16 -> FP32) or kind::tf32 (TF32 x TF32 -> FP32); a_mn / b_mn select
+// MN-major operands (valid for both source formats).  Source format field: 1 = BF16, 2 = TF32.
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n, bool a_mn, bool b_mn, bool tf32) {
     return (1u << 4)                      // D format F32
-           | (1u << 7)                    // A format BF16
-           | (1u << 10)                   // B format BF16
+           | ((tf32 ? 2u : 1u) << 7)      // A format
+           | ((tf32 ? 2u : 1u) << 10)     // B format
            | ((a_mn ? 1u : 0u) << 15)     // A major: 0 = K, 1 = MN
            | ((b_mn ? 1u : 0u) << 16)     // B major
            | ((uint32_t)(n >> 3) << 17)   // N / 8

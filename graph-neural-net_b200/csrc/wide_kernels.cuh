@@ -74,14 +74,38 @@ __device__ __forceinline__ void load8_as_float<uint8_t>(const uint8_t *x, float 
     }
 }
 
+// operand-type stores: BF16 nets keep activations / deltas as BF16, TF32 nets as FP32
+__device__ __forceinline__ void store8(__nv_bfloat16 *o, const float (&v)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+    u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4 *>(o) = u;
+}
+__device__ __forceinline__ void store8(float *o, const float (&v)[8]) {
+    reinterpret_cast<float4 *>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4 *>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16 *o, float a, float b, float c, float d) {
+    *reinterpret_cast<uint2 *>(o) = make_uint2(pack_bf16x2(a, b), pack_bf16x2(c, d));
+}
+__device__ __forceinline__ void store4(float *o, float a, float b, float c, float d) {
+    *reinterpret_cast<float4 *>(o) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void store2(__nv_bfloat16 *o, float a, float b) {
+    *reinterpret_cast<uint32_t *>(o) = pack_bf16x2(a, b);
+}
+__device__ __forceinline__ void store2(float *o, float a, float b) { *reinterpret_cast<float2 *>(o) = make_float2(a, b); }
+__device__ __forceinline__ void store1(__nv_bfloat16 *o, float a) { *o = __float2bfloat16_rn(a); }
+__device__ __forceinline__ void store1(float *o, float a) { *o = a; }
+
 // a0 = f(x) (the reference activates the INPUT layer too, SoftmaxCrossEntropyNeuralNet.java:183-186)
-// for the rows named by idx (or rows 0..B-1), cast to BF16, stored [B][ld_a].
+// for the rows named by idx (or rows 0..B-1), cast to the operand type O (BF16, or FP32 for TF32 nets), stored [B][ld_a].
 // X may live in HBM or in mapped pinned host memory (then this kernel IS the host->device copy).
 // One thread per 8 consecutive elements of a row (one 16-byte store); grid-stride over B * ceil(d0/8).
-template <typename T>
+template <typename T, typename O = __nv_bfloat16>
 __global__ void __launch_bounds__(256)
 input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, int d0, int act, float act_param,
-               __nv_bfloat16 *__restrict__ a, int ld_a) {
+               O *__restrict__ a, int ld_a) {
     const int groups = (d0 + 7) >> 3;
     const long long total = (long long)B * groups;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
@@ -89,18 +113,15 @@ input_prologue(const T *__restrict__ X, const int32_t *__restrict__ idx, int B, 
         const int b = (int)(t / groups), i0 = (int)(t % groups) * 8;
         const long long src = idx ? idx[b] : b;
         const T *x = X + src * d0 + i0;
-        __nv_bfloat16 *o = a + (size_t)b * ld_a + i0;
+        O *o = a + (size_t)b * ld_a + i0;
         if (i0 + 8 <= d0) {
             float v[8];
             load8_as_float<T>(x, v);
 #pragma unroll
             for (int e = 0; e < 8; e++) v[e] = act_apply(act, act_param, v[e]);
-            uint4 u;
-            u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
-            u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
-            *reinterpret_cast<uint4 *>(o) = u;
+            store8(o, v);
         } else {
-            for (int e = 0; i0 + e < d0; e++) o[e] = __float2bfloat16_rn(act_apply(act, act_param, load_as_float<T>(x + e)));
+            for (int e = 0; i0 + e < d0; e++) store1(o + e, act_apply(act, act_param, load_as_float<T>(x + e)));
         }
     }
 }
@@ -151,11 +172,12 @@ __device__ __forceinline__ float warp_sum(float v) {
 //  kind 0: p = softmax(z) (max-subtracted: identical maths, SoftmaxCrossEntropyNeuralNet.java:357-376),
 //          loss = -sum t log p (:213-217), delta = p - t (:249-251); t one-hot from labels or dense.
 //  kind 1: a = f_last(z); loss = sum L(a,t); delta = L'(a,t) f_last'(z) (GeneralNeuralNet.java:236-239,268-271).
-// Writes delta as BF16 d[B][ld_d]; row_loss[B] FP32.
+// Writes delta in the operand type O (BF16, or FP32 for TF32 nets) d[B][ld_d]; row_loss[B] FP32.
+template <typename O>
 __global__ void __launch_bounds__(256)
 output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ labels,
              const float *__restrict__ tdense, int ld_t, int B, int dL, int kind, int last_act, float last_param,
-             __nv_bfloat16 *__restrict__ d, int ld_d, float *__restrict__ row_loss, double *loss_slot,
+             O *__restrict__ d, int ld_d, float *__restrict__ row_loss, double *loss_slot,
              double *__restrict__ block_partial, unsigned int *block_counter) {
     __shared__ float s_row[8];
     __shared__ bool s_last;
@@ -166,7 +188,7 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
     const float *z = Z + (size_t)b * ld_z;
     const float *t = tdense ? tdense + (size_t)b * ld_t : nullptr;
     const int lab = labels ? labels[b] : -1;
-    __nv_bfloat16 *drow = d + (size_t)b * ld_d;
+    O *drow = d + (size_t)b * ld_d;
     float mx = 0.f, inv = 1.f, lse = 0.f;
     if (kind == 0 && t == nullptr && dL <= 1024 && ((ld_z | ld_d) & 3) == 0) {
         // softmax / cross-entropy with labels, row held in registers: ONE pass over global memory, 16-byte loads
@@ -208,11 +230,11 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
             if (lab == c + 1) p1 -= 1.f;
             if (lab == c + 2) p2 -= 1.f;
             if (lab == c + 3) p3 -= 1.f;
-            if (c + 4 <= dL) *reinterpret_cast<uint2 *>(drow + c) = make_uint2(pack_bf16x2(p0, p1), pack_bf16x2(p2, p3));
+            if (c + 4 <= dL) store4(drow + c, p0, p1, p2, p3);
             else {
-                drow[c] = __float2bfloat16_rn(p0);
-                if (c + 1 < dL) drow[c + 1] = __float2bfloat16_rn(p1);
-                if (c + 2 < dL) drow[c + 2] = __float2bfloat16_rn(p2);
+                store1(drow + c, p0);
+                if (c + 1 < dL) store1(drow + c + 1, p1);
+                if (c + 2 < dL) store1(drow + c + 2, p2);
             }
         }
         lacc = warp_sum(lacc);
@@ -249,8 +271,8 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
                 }
             }
         }
-        if (c0 + 1 < dL) *reinterpret_cast<uint32_t *>(drow + c0) = pack_bf16x2(dv[0], dv[1]);
-        else drow[c0] = __float2bfloat16_rn(dv[0]);
+        if (c0 + 1 < dL) store2(drow + c0, dv[0], dv[1]);
+        else store1(drow + c0, dv[0]);
     }
     lacc = warp_sum(lacc);
     if (lane == 0 && row_loss) row_loss[b] = lacc;
@@ -326,6 +348,7 @@ __global__ void eval_rows(const float *__restrict__ Z, int ld_z, const int32_t *
 // Momentum-SGD update (SoftmaxCrossEntropyNeuralNet.java:325-342) over the padded [in][ld_n] arrays as one
 // flat stream of float4: v = scale*g + mu*v ; w -= v ; emit the BF16 operand copy wn.  Algorithmic traffic
 // 12 B read + 10 B written per parameter.  cast_only: just (re)build wn from the master weights.
+// wn == nullptr (TF32 nets: the FP32 master array IS the GEMM operand): no copy is written, 12 B + 8 B.
 __global__ void __launch_bounds__(256)
 sgd_update(const float4 *__restrict__ g, float4 *__restrict__ w, float4 *__restrict__ v, long long n4, float scale,
            float momentum, int cast_only, uint2 *__restrict__ wn) {
@@ -341,7 +364,7 @@ sgd_update(const float4 *__restrict__ g, float4 *__restrict__ w, float4 *__restr
             v[q] = vv;
             w[q] = wv;
         }
-        wn[q] = make_uint2(pack_bf16x2(wv.x, wv.y), pack_bf16x2(wv.z, wv.w));
+        if (wn) wn[q] = make_uint2(pack_bf16x2(wv.x, wv.y), pack_bf16x2(wv.z, wv.w));
     }
 }
 

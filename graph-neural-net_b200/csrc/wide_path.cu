@@ -1,4 +1,4 @@
-// wide_path.cu -- host orchestration of the BF16 tensor-core path: per-step sequence of
+// wide_path.cu -- host orchestration of the tensor-core path (BF16 or TF32 operands): per-step sequence of
 // tcgen05 GEMMs (gemm_tcgen05.cuh) and the HBM-bound kernels around them (wide_kernels.cuh).
 // Data layout in HBM (per layer l with W_l: d_l x d_{l+1}):
 //   w, v, g  FP32 [d_l][pad8(d_{l+1})]   master weights / velocity / summed gradient (boundary layout, padded)
@@ -6,6 +6,8 @@
 //   a[l]     BF16 [B][pad8(d_l)]         activations (K-major A forward, MN-major A gradient)
 //   d[l]     BF16 [B][pad8(d_l)]         deltas      (K-major A delta,   MN-major B gradient)
 // No transposed copies exist: UMMA reads either major-ness from the same row-major buffer.
+// B2NN_PREC_TF32 nets: a[l], d[l] are FP32 arrays of the same shapes, wn does not exist and the GEMMs read the
+// FP32 master w directly (tcgen05 kind::tf32 ignores the low mantissa bits TMA did not round away).
 #include "wide_path.hpp"
 
 #include "comm.hpp"
@@ -32,18 +34,27 @@ static PFN_tmapEncodeTiled get_encode_fn() {
     return fn;
 }
 
-// One map per BF16 buffer [rows][ld] with `inner` valid elements per row: 64 x 64 box, 128-byte swizzle
-// (matches make_desc_kmajor_sw128 / make_desc_mnmajor_sw128), out-of-bounds elements read as zero.
-int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld) {
+// One map per operand buffer [rows][ld] with `inner` valid elements per row: a square box whose rows are 128 bytes
+// (64 x 64 BF16, 32 x 32 FP32-as-TF32), 128-byte swizzle (matches make_desc_kmajor_sw128 /
+// make_desc_mnmajor_sw128; TF32 buffers read MN-major get the 32-byte-atom swizzle of
+// make_desc_mnmajor_sw128_base32b instead), out-of-bounds elements read as zero.  The TFLOAT32 map type makes TMA round the FP32
+// words to TF32 on the way into shared memory (the tensor core would otherwise truncate them).
+int make_tmap(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld, bool tf32, bool mn_major) {
     PFN_tmapEncodeTiled fn = get_encode_fn();
     B2_REQUIRE(fn != nullptr, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    const cuuint32_t edge = tf32 ? (cuuint32_t)GemmCfg<true>::CH : (cuuint32_t)GemmCfg<false>::CH;
     cuuint64_t gdim[2] = {inner, rows};
-    cuuint64_t gstride[1] = {ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, 64};
+    cuuint64_t gstride[1] = {ld * (tf32 ? 4u : 2u)};
+    cuuint32_t box[2] = {edge, edge};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    static const bool plain_f32 = getenv("B2NN_TF32_TMAP") && getenv("B2NN_TF32_TMAP")[0] == 'f';  // debug
+    CUresult r = fn(m, tf32 ? (plain_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32)
+                            : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                    const_cast<void *>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    // kind::tf32 reads MN-major operands only from the 32-byte-atom flavour of the 128-byte swizzle
+                    (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B2_REQUIRE(r == CUDA_SUCCESS, B2NN_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (inner=%llu rows=%llu ld=%llu)",
                (int)r, (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)ld);
     return B2NN_OK;
@@ -93,12 +104,21 @@ int profile_flush(b2nn_net *net) {
     return B2NN_OK;
 }
 
-template <int EPI, bool A_MN, bool B_MN>
-static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+static inline bool is_tf32(const b2nn_net *net) { return net->precision == B2NN_PREC_TF32; }
+
+typedef void (*GemmKernel)(const CUtensorMap, const CUtensorMap, const GemmArgs);
+template <int EPI, bool A_MN, bool B_MN, bool TF32>
+static GemmKernel gemm_kernel() {
+    if constexpr (TF32) return gemm_tf32_pair_kernel<EPI, A_MN, B_MN>;
+    else return gemm_bf16_pair_kernel<EPI, A_MN, B_MN>;
+}
+
+template <int EPI, bool A_MN, bool B_MN, bool TF32>
+static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+    const GemmKernel kernel = gemm_kernel<EPI, A_MN, B_MN, TF32>();
     static bool attr_done = false;
     if (!attr_done) {
-        B2_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_pair_kernel<EPI, A_MN, B_MN>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+        B2_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
         attr_done = true;
     }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -113,6 +133,7 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
     GemmArgs ga = g;
     ga.tile_counter = net->dynamic_tiles ? net->tile_counter : nullptr;
+    ga.dbg = getenv("B2NN_GEMM_DBG") ? atoi(getenv("B2NN_GEMM_DBG")) : 0;  // debug, read per launch
     static const bool want_stalls = getenv("B2NN_GEMM_STALLS") != nullptr;  // debug: where the role warps wait
     static unsigned int *stalls_dev = nullptr;
     if (want_stalls) {
@@ -120,7 +141,7 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
         B2_CHECK_CUDA(cudaMemsetAsync(stalls_dev, 0, 8 * 148 * 2 * sizeof(unsigned int), net->stream));
         ga.stalls = stalls_dev;
     }
-    gemm_bf16_pair_kernel<EPI, A_MN, B_MN><<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
+    kernel<<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
     if (want_stalls) {
         static int printed = 0;
         std::vector<unsigned int> h(8 * 2 * pairs);
@@ -143,6 +164,14 @@ static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
+}
+
+template <int EPI, bool A_MN, bool B_MN>
+static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
+    if constexpr (EPI != EPI_DW_UPDATE) {
+        if (is_tf32(net)) return launch_gemm_t<EPI, A_MN, B_MN, true>(net, ta, tb, g);
+    }
+    return launch_gemm_t<EPI, A_MN, B_MN, false>(net, ta, tb, g);
 }
 
 static int launch_update(b2nn_net *net, WideLayer &y, float scale, float momentum, int cast_only, cudaStream_t st) {
@@ -169,7 +198,7 @@ int wide_upload_weights(b2nn_net *net, const double *w_flat, bool velocity) {
         B2_CHECK_CUDA(cudaMemcpyAsync(velocity ? y.v : y.w, tmp.data(), tmp.size() * sizeof(float),
                                       cudaMemcpyHostToDevice, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
-        if (!velocity) B2_TRY(launch_update(net, y, 0.f, 0.f, 1, net->stream));
+        if (!velocity && y.wn) B2_TRY(launch_update(net, y, 0.f, 0.f, 1, net->stream));  // rebuild the BF16 copy
     }
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     return B2NN_OK;
@@ -219,7 +248,13 @@ static int prefer_max_shared_carveout() {
                                        cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue<uint8_t>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::input_prologue_u8x16, cudaFuncAttributePreferredSharedMemoryCarveout, c));
-    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::output_delta, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::output_delta<__nv_bfloat16>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::output_delta<float>, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute((wide::input_prologue<double, float>), cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute((wide::input_prologue<float, float>), cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute((wide::input_prologue<__nv_bfloat16, float>),
+                                       cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    B2_CHECK_CUDA(cudaFuncSetAttribute((wide::input_prologue<uint8_t, float>), cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::reduce_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_labels, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_targets, cudaFuncAttributePreferredSharedMemoryCarveout, c));
@@ -241,7 +276,7 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         y.in = net->dims[l]; y.out = net->dims[l + 1];
         y.ld_n = pad8(y.out);
         const size_t nf = (size_t)y.in * y.ld_n;
-        bytes += 3 * up(nf * sizeof(float)) + up(nf * sizeof(__nv_bfloat16));
+        bytes += 3 * up(nf * sizeof(float)) + (is_tf32(net) ? 0 : up(nf * sizeof(__nv_bfloat16)));
     }
     B2_CHECK_CUDA(cudaMalloc(&net->arena, bytes));
     B2_CHECK_CUDA(cudaMemset(net->arena, 0, bytes));
@@ -253,8 +288,15 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         y.g = (float *)(net->arena + off); off += up(nf * sizeof(float));
         y.w = (float *)(net->arena + off); off += up(nf * sizeof(float));
         y.v = (float *)(net->arena + off); off += up(nf * sizeof(float));
-        y.wn = (__nv_bfloat16 *)(net->arena + off); off += up(nf * sizeof(__nv_bfloat16));
-        B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
+        if (is_tf32(net)) {
+            y.wn = nullptr;  // the FP32 master array is the operand
+            B2_TRY(make_tmap(&y.tm_w, y.w, y.out, y.in, y.ld_n, true, false));
+            B2_TRY(make_tmap(&y.tm_w_mn, y.w, y.out, y.in, y.ld_n, true, true));
+        } else {
+            y.wn = (__nv_bfloat16 *)(net->arena + off); off += up(nf * sizeof(__nv_bfloat16));
+            B2_TRY(make_tmap(&y.tm_w, y.wn, y.out, y.in, y.ld_n, false));
+            y.tm_w_mn = y.tm_w;
+        }
     }
     // side stream: the HBM-bound update (and, data-parallel, the all-reduce before it) of layer l runs there
     // while the tensor cores go on with layer l-1's contractions
@@ -284,8 +326,14 @@ int wide_rebase_arena(b2nn_net *net, char *new_base) {
         y.g = (float *)(new_base + ((char *)y.g - old));
         y.w = (float *)(new_base + ((char *)y.w - old));
         y.v = (float *)(new_base + ((char *)y.v - old));
-        y.wn = (__nv_bfloat16 *)(new_base + ((char *)y.wn - old));
-        B2_TRY(make_tmap_bf16(&y.tm_w, y.wn, y.out, y.in, y.ld_n));
+        if (y.wn) {
+            y.wn = (__nv_bfloat16 *)(new_base + ((char *)y.wn - old));
+            B2_TRY(make_tmap(&y.tm_w, y.wn, y.out, y.in, y.ld_n, false));
+            y.tm_w_mn = y.tm_w;
+        } else {
+            B2_TRY(make_tmap(&y.tm_w, y.w, y.out, y.in, y.ld_n, true, false));
+            B2_TRY(make_tmap(&y.tm_w_mn, y.w, y.out, y.in, y.ld_n, true, true));
+        }
     }
     net->arena = new_base;
     return B2NN_OK;
@@ -334,6 +382,7 @@ void wide_use_slot(b2nn_net *net, int q) {
     WideBatch &b = net->wb;
     b.a[0] = b.a0_slot[q];
     b.tm_a[0] = b.tm_a0_slot[q];
+    b.tm_a_mn[0] = b.tm_a0_slot_mn[q];
     b.labels = b.labels_slot[q];
 }
 
@@ -343,26 +392,31 @@ int wide_ensure_batch(b2nn_net *net, int B) {
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     free_batch(net);
     const int nd = net->n_dims, L = nd - 1;
+    const bool tf32 = is_tf32(net);
+    const size_t es = tf32 ? 4 : 2;  // operand element size
     b.a.assign(nd, nullptr); b.d.assign(nd, nullptr);
-    b.tm_a.resize(nd); b.tm_d.resize(nd);
+    b.tm_a.resize(nd); b.tm_d.resize(nd); b.tm_a_mn.resize(nd); b.tm_d_mn.resize(nd);
     for (int l = 0; l < nd; l++) {
         const int dl = net->dims[l], ld = pad8(dl);
         if (l == 0) {
             for (int q = 0; q < 2; q++) {
-                B2_CHECK_CUDA(cudaMalloc(&b.a0_slot[q], (size_t)B * ld * 2));
-                B2_CHECK_CUDA(cudaMemset(b.a0_slot[q], 0, (size_t)B * ld * 2));
-                B2_TRY(make_tmap_bf16(&b.tm_a0_slot[q], b.a0_slot[q], dl, B, ld));
+                B2_CHECK_CUDA(cudaMalloc(&b.a0_slot[q], (size_t)B * ld * es));
+                B2_CHECK_CUDA(cudaMemset(b.a0_slot[q], 0, (size_t)B * ld * es));
+                B2_TRY(make_tmap(&b.tm_a0_slot[q], b.a0_slot[q], dl, B, ld, tf32, false));
+                B2_TRY(make_tmap(&b.tm_a0_slot_mn[q], b.a0_slot[q], dl, B, ld, tf32, true));
                 B2_CHECK_CUDA(cudaMalloc(&b.labels_slot[q], (size_t)B * sizeof(int32_t)));
             }
         } else if (l < L) {
-            B2_CHECK_CUDA(cudaMalloc(&b.a[l], (size_t)B * ld * 2));
-            B2_CHECK_CUDA(cudaMemset(b.a[l], 0, (size_t)B * ld * 2));
-            B2_TRY(make_tmap_bf16(&b.tm_a[l], b.a[l], dl, B, ld));
+            B2_CHECK_CUDA(cudaMalloc(&b.a[l], (size_t)B * ld * es));
+            B2_CHECK_CUDA(cudaMemset(b.a[l], 0, (size_t)B * ld * es));
+            B2_TRY(make_tmap(&b.tm_a[l], b.a[l], dl, B, ld, tf32, false));
+            B2_TRY(make_tmap(&b.tm_a_mn[l], b.a[l], dl, B, ld, tf32, true));
         }
         if (l >= 1) {
-            B2_CHECK_CUDA(cudaMalloc(&b.d[l], (size_t)B * ld * 2));
-            B2_CHECK_CUDA(cudaMemset(b.d[l], 0, (size_t)B * ld * 2));
-            B2_TRY(make_tmap_bf16(&b.tm_d[l], b.d[l], dl, B, ld));
+            B2_CHECK_CUDA(cudaMalloc(&b.d[l], (size_t)B * ld * es));
+            B2_CHECK_CUDA(cudaMemset(b.d[l], 0, (size_t)B * ld * es));
+            B2_TRY(make_tmap(&b.tm_d[l], b.d[l], dl, B, ld, tf32, false));
+            B2_TRY(make_tmap(&b.tm_d_mn[l], b.d[l], dl, B, ld, tf32, true));
         }
     }
     const int ldL = pad8(net->dims[L]);
@@ -398,29 +452,39 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     }
     if (const char *e = getenv("B2NN_PROLOGUE_THREADS")) { thr = atoi(e); grid = net->num_sms * blocks_per_sm; }
     const float p = (float)net->inner_param;
+    const int act = net->inner_act, ld = pad8(d0);
+    if (is_tf32(net)) {  // FP32 operand rows
+        float *a0 = (float *)b.a[0];
+        switch (x_dtype) {
+        case B2NN_DT_F64: wide::input_prologue<double, float><<<grid, thr, 0, st>>>((const double *)X, idx_dev, B, d0, act, p, a0, ld); break;
+        case B2NN_DT_F32: wide::input_prologue<float, float><<<grid, thr, 0, st>>>((const float *)X, idx_dev, B, d0, act, p, a0, ld); break;
+        case B2NN_DT_BF16:
+            wide::input_prologue<__nv_bfloat16, float><<<grid, thr, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0, act, p, a0, ld);
+            break;
+        case B2NN_DT_U8: wide::input_prologue<uint8_t, float><<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, act, p, a0, ld); break;
+        default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
+        }
+    } else {
+    __nv_bfloat16 *a0 = (__nv_bfloat16 *)b.a[0];
     switch (x_dtype) {
     case B2NN_DT_F64:
-        wide::input_prologue<double><<<grid, thr, 0, st>>>((const double *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
-                                                          pad8(d0));
+        wide::input_prologue<double><<<grid, thr, 0, st>>>((const double *)X, idx_dev, B, d0, act, p, a0, ld);
         break;
     case B2NN_DT_F32:
-        wide::input_prologue<float><<<grid, thr, 0, st>>>((const float *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
-                                                         pad8(d0));
+        wide::input_prologue<float><<<grid, thr, 0, st>>>((const float *)X, idx_dev, B, d0, act, p, a0, ld);
         break;
     case B2NN_DT_BF16:
-        wide::input_prologue<__nv_bfloat16><<<grid, thr, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0,
-                                                                 net->inner_act, p, b.a[0], pad8(d0));
+        wide::input_prologue<__nv_bfloat16><<<grid, thr, 0, st>>>((const __nv_bfloat16 *)X, idx_dev, B, d0, act, p, a0, ld);
         break;
     case B2NN_DT_U8:
         if (d0 % 16 == 0) {
-            wide::input_prologue_u8x16<<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, net->inner_act, p,
-                                                             b.a[0], pad8(d0));
+            wide::input_prologue_u8x16<<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, act, p, a0, ld);
             break;
         }
-        wide::input_prologue<uint8_t><<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, net->inner_act, p, b.a[0],
-                                                           pad8(d0));
+        wide::input_prologue<uint8_t><<<grid, thr, 0, st>>>((const uint8_t *)X, idx_dev, B, d0, act, p, a0, ld);
         break;
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
+    }
     }
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
@@ -442,10 +506,10 @@ int wide_forward(b2nn_net *net, int B) {
         g.act = net->inner_act; g.act_param = (float)net->inner_param;
         if (l + 1 < L) {
             g.out0 = b.a[l + 1]; g.ld0 = pad8(y.out);
-            B2_TRY((launch_gemm<EPI_ACT, false, true>(net, b.tm_a[l], y.tm_w, g)));
+            B2_TRY((launch_gemm<EPI_ACT, false, true>(net, b.tm_a[l], y.tm_w_mn, g)));
         } else {
             g.out0 = b.logits; g.ld0 = pad8(y.out);
-            B2_TRY((launch_gemm<EPI_LOGITS, false, true>(net, b.tm_a[l], y.tm_w, g)));
+            B2_TRY((launch_gemm<EPI_LOGITS, false, true>(net, b.tm_a[l], y.tm_w_mn, g)));
         }
         trace_mark(net, net->stream, "fwd", l);
     }
@@ -456,9 +520,16 @@ int wide_forward(b2nn_net *net, int B) {
 int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1, dL = net->dims[L], ldL = pad8(dL);
-    wide::output_delta<<<(B + 7) / 8, 256, 0, net->stream>>>(
-        b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
-        net->last_act, (float)net->last_param, b.d[L], ldL, b.row_loss, loss_slot_dev, b.block_partial, b.block_counter);
+    if (is_tf32(net))
+        wide::output_delta<float><<<(B + 7) / 8, 256, 0, net->stream>>>(
+            b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
+            net->last_act, (float)net->last_param, (float *)b.d[L], ldL, b.row_loss, loss_slot_dev, b.block_partial,
+            b.block_counter);
+    else
+        wide::output_delta<__nv_bfloat16><<<(B + 7) / 8, 256, 0, net->stream>>>(
+            b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
+            net->last_act, (float)net->last_param, (__nv_bfloat16 *)b.d[L], ldL, b.row_loss, loss_slot_dev,
+            b.block_partial, b.block_counter);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -489,14 +560,14 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
     GemmArgs g{};
     g.M = y.in; g.N = y.out; g.K = B;
     g.ldw = y.ld_n;
-    if (net->world == 1 && net->fused_update) {
+    if (net->world == 1 && net->fused_update && !is_tf32(net)) {
         g.w = y.w; g.v = y.v;
         g.out0 = y.wn; g.ld0 = y.ld_n;
         g.scale = scale; g.momentum = momentum;
-        return launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g);
+        return launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g);
     }
     g.w = y.g;
-    B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a[l], b.tm_d[l + 1], g)));
+    B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g)));
     trace_mark(net, net->stream, "dW", l);
     if (us != net->stream) {
         B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
@@ -558,7 +629,7 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
     const float mu = (float)momentum;
     // with b2nn_profile_enable on, everything runs in stream order so that the event pairs time each contraction alone
     const bool side = (net->world > 1 || net->overlap_update) && !net->profiling;
-    if (net->backward_reorder && !net->fused_update) {
+    if (net->backward_reorder && !(net->fused_update && !is_tf32(net))) {
         for (int l = L - 1; l >= 1; l--) B2_TRY(launch_delta(net, l, B));
         for (int l = 0; l < L; l++)
             B2_TRY(launch_gradient_and_update(net, l, B, scale, mu, side ? net->aux_stream : net->stream));

@@ -1,10 +1,10 @@
-// wide_path.hpp -- BF16 tensor-core path entry points (see wide_path.cu)
+// wide_path.hpp -- tensor-core path (BF16 / TF32 operands) entry points (see wide_path.cu)
 #pragma once
 #include "common.hpp"
 
 namespace b2nn {
 struct GemmArgs;
-int make_tmap_bf16(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld);
+int make_tmap(CUtensorMap *m, const void *base, uint64_t inner, uint64_t rows, uint64_t ld, bool tf32, bool mn_major = false);
 int profile_flush(b2nn_net *net);
 void trace_mark(b2nn_net *net, cudaStream_t st, const char *label, int l);
 void trace_dump(b2nn_net *net, int first, int count);

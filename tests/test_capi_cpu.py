@@ -57,8 +57,11 @@ def test_constructor_argument_errors(g):
     with pytest.raises(ValueError):
         g.GeneralNeuralNet([4, 2], g.SIGMOID, g.SIGMOID_PRIME, g.SIGMOID, g.SIGMOID_PRIME,
                            lambda c, e: 0.0, lambda c, e: 0.0)
-    with pytest.raises(NotImplementedError):                                          # TF32 reserved
+    with pytest.raises(ValueError):                                                   # unknown precision enum
+        g.SoftmaxCrossEntropyNeuralNet([4, 2], g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=7)
+    with pytest.raises(g.capi.B2nnError) as e:                                        # TF32 is a real mode: needs a GPU
         g.SoftmaxCrossEntropyNeuralNet([4, 2], g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_TF32)
+    assert e.value.code == g.capi.ERR_NO_DEVICE
 
 
 def test_function_singletons_match_oracle_scalars(g, orc):
