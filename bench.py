@@ -206,14 +206,19 @@ def run_b2nn(args):
     wl = WORKLOADS[args.workload]
     dims, B = wl["dims"], wl["batch"]
     K, W = args.steps, args.warmup
-    bf16 = wl["prec"] == "bf16"
+    bf16 = wl["prec"] == "bf16"                      # a tensor-core ("wide") workload
+    tf32 = bf16 and args.precision == "tf32"         # ... computed with TF32 operands instead of BF16
+    if tf32 and world > 1:
+        raise SystemExit("--precision tf32 is single-GPU (TF32 nets have no data-parallel exchange)")
+    prec_name = "tf32" if tf32 else wl["prec"]
 
     sampler_thread = ClockSampler(local_rank)
     sampler_thread.start()
 
     def make_net():
         if bf16:
-            return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+            return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME,
+                                                  precision=g.capi.PREC_TF32 if tf32 else g.capi.PREC_BF16,
                                                   flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX,
                                                   device=local_rank)
         return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
@@ -289,13 +294,16 @@ def run_b2nn(args):
         net.profileEnable(False)
         prof_step_ms = ev2.elapsed_time(ev3) / K
         pk = measured_peaks()
+        if tf32:
+            # MEASURED_PEAKS.json holds no TF32 figure: the profiling recipe's nominal dense TF32 peak stands in
+            pk = dict(pk, tflops=1100.0, src="nominal dense TF32 peak (B200_PROFILING.md); no measured TF32 peak on file")
         achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             with open(tp) as f:
-                traffic = json.load(f).get(args.workload)
-        roof = {"bound": "tensor", "kernel": "gemm_bf16_pair_kernel (tcgen05 cta_group::2, all epilogues)", "achieved": achieved,
+                traffic = json.load(f).get(args.workload + ("_tf32" if tf32 else ""))
+        roof = {"bound": "tensor", "kernel": "gemm_%s_pair_kernel (tcgen05 cta_group::2, all epilogues)" % prec_name, "achieved": achieved,
                 "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "peak_source": pk["src"],
                 "traffic": traffic, "launches": gemm_n, "avg_launch_ms": gemm_ms / max(gemm_n, 1),
                 "flops_per_step": float(B * flops_per_sample(dims)),
@@ -317,6 +325,8 @@ def run_b2nn(args):
         if args.e2e_rows == "u8":
             # rows in the reference's own storage format, IDX pixel bytes read as (raw & 0xff) / 255.0 (M:97)
             x_host = np.minimum(np.floor(x * 256.0), 255.0).astype(np.uint8)
+        elif tf32:
+            x_host = x                                   # FP32 rows: the operand container of this mode
         else:
             u = x.view(np.uint32)
             x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
@@ -337,7 +347,7 @@ def run_b2nn(args):
     e2e = {"value": world * B * K / e2e_s, "unit": "samples/s",
            "h2d_bytes_per_step": (x_host_bytes if bf16 else 0) + B * 4, "d2h_bytes_per_step": 8,
            "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]),
-           "rows": args.e2e_rows if bf16 else "f64",
+           "rows": ("u8" if args.e2e_rows == "u8" else "f32" if tf32 else "bf16") if bf16 else "f64",
            "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset of BF16 (or, with --e2e-rows u8, pixel-byte) rows: every step's batch rows are "
                     "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
                     "(double-buffered under the previous step's GEMMs); per-step loss read back" if bf16 else
@@ -364,8 +374,9 @@ def run_b2nn(args):
         out = {
             "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": wl["prec"], "data": "synthetic",
-            "config": {"workload": args.workload + ": " + wl["desc"], "dims": dims, "batch_per_gpu": B,
+            "dtype": prec_name, "data": "synthetic",
+            "config": {"workload": args.workload + ": " + (wl["desc"].replace("BF16", "TF32") if tf32 else wl["desc"]),
+                       "dims": dims, "batch_per_gpu": B,
                        "global_batch": B * world, "parallelism": "dp%d" % world,
                        "exchange": net.commMode() if bf16 else "single",
                        "l2": "no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh "
@@ -423,6 +434,8 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-rows", default="bf16", choices=["bf16", "u8"],
                     help="element type of the pinned host rows of the e2e leg (u8 = IDX pixel bytes / 255)")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
+                    help="operand type of the tensor-core workloads c4 / c5 (tf32: single GPU)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the 784-300-100-10 side measurement")
     args = ap.parse_args()

@@ -79,7 +79,8 @@ enum b2nn_loss_kind {
 enum b2nn_precision {
     B2NN_PREC_F64 = 0,  /* parity mode: double everywhere, like the JVM */
     B2NN_PREC_BF16 = 1, /* tcgen05 kind::f16 GEMMs, FP32 accumulate, FP32 master W and V */
-    B2NN_PREC_TF32 = 2  /* tcgen05 kind::tf32 GEMMs (reserved; UNSUPPORTED until implemented) */
+    B2NN_PREC_TF32 = 2  /* tcgen05 kind::tf32 GEMMs over FP32 activations / deltas / master weights (no operand
+                         * copy), FP32 accumulate; single GPU (b2nn_comm_init returns UNSUPPORTED) */
 };
 
 enum b2nn_flags {
@@ -92,7 +93,7 @@ enum b2nn_flags {
 };
 
 /* element type of dataset rows handed to b2nn_dataset_create.  B2NN_DT_U8 rows are IDX pixel bytes, read as
- * (raw & 0xff) / 255.0 exactly like the reference's loader (MNISTTrainer.java:97); BF16 nets only (FP64 nets take
+ * (raw & 0xff) / 255.0 exactly like the reference's loader (MNISTTrainer.java:97); BF16 / TF32 nets only (FP64 nets take
  * the doubles and find the bytes themselves). */
 enum b2nn_dtype { B2NN_DT_F64 = 0, B2NN_DT_F32 = 1, B2NN_DT_BF16 = 2, B2NN_DT_U8 = 3 };
 
@@ -132,7 +133,7 @@ int b2nn_weight_gradient(b2nn_net *net, const double *x, const double *t, double
 int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t B,
                        double step, double momentum, int32_t noise,
                        double *mean_loss_or_null);
-/* same step for one-hot targets and narrower host dtypes (wide nets): x is
+/* same step for one-hot targets and narrower host dtypes (BF16 / TF32 nets): x is
  * [B][d0] of x_dtype, labels [B] class ids.  SOFTMAX_CE nets only. */
 int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype,
                                const int32_t *labels, int32_t B, double step,

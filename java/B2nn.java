@@ -22,7 +22,7 @@ import static java.lang.foreign.ValueLayout.JAVA_LONG;
 final class B2nn {
 	static final int OK = 0, ERR_INVALID_ARG = -1, ERR_DIM_MISMATCH = -2, ERR_UNSUPPORTED = -3;
 	static final int NET_SOFTMAX_CE = 0, NET_GENERAL = 1;
-	static final int PREC_F64 = 0, PREC_BF16 = 1;
+	static final int PREC_F64 = 0, PREC_BF16 = 1, PREC_TF32 = 2;
 	static final int DT_F64 = 0;
 	static final int DATA_DEVICE = 0;
 
