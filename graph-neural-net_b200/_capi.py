@@ -36,6 +36,10 @@ SIGNATURES = {
     "b2nn_set_weights": (C.c_int, [_vp, _dp]),
     "b2nn_get_velocity": (C.c_int, [_vp, _dp]),
     "b2nn_set_velocity": (C.c_int, [_vp, _dp]),
+    "b2nn_time": (C.c_int, [_vp, _lp]),
+    "b2nn_checkpoint_save": (C.c_int, [_vp, C.c_char_p]),
+    "b2nn_checkpoint_load": (C.c_int, [_vp, C.c_char_p]),
+    "b2nn_checkpoint_info": (C.c_int, [C.c_char_p, _ip, _ip, C.c_int32, _ip, _ip, _lp, _lp]),
     "b2nn_dataset_create": (C.c_int, [_vp, _vp, C.c_int32, _dp, _ip, C.c_int64, C.c_int32, C.POINTER(_vp)]),
     "b2nn_dataset_destroy": (C.c_int, [_vp]),
     "b2nn_train_indexed": (C.c_int, [_vp, _vp, _ip, C.c_int32, C.c_int32, C.c_double, C.c_double, _dp]),
@@ -100,6 +104,20 @@ def check(code):
     if code == ERR_UNSUPPORTED:
         raise NotImplementedError("b2nn: " + msg)
     raise B2nnError(code, msg)
+
+
+def checkpoint_info(path):
+    """header of a checkpoint file (b2nn_checkpoint_info; host only): dict with layerDims, kind, precision, time,
+    numWeights"""
+    import numpy as np
+    nd, kind, prec = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+    t, nw = C.c_int64(0), C.c_int64(0)
+    p = os.fsencode(path)
+    check(lib().b2nn_checkpoint_info(p, C.byref(nd), None, 0, C.byref(kind), C.byref(prec), C.byref(t), C.byref(nw)))
+    dims = np.zeros(nd.value, dtype=np.int32)
+    check(lib().b2nn_checkpoint_info(p, None, dims.ctypes.data_as(_ip), nd.value, None, None, None, None))
+    return {"layerDims": [int(d) for d in dims], "kind": kind.value, "precision": prec.value, "time": t.value,
+            "numWeights": nw.value}
 
 
 def device_count():

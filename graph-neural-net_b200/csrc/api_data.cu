@@ -267,6 +267,7 @@ int b2nn_train_indexed(b2nn_net *net, b2nn_dataset *ds, const int32_t *idx, int3
         }
     }
     if (is_wide_precision(net->precision)) B2_TRY(wide_join(net));  // side-stream updates belong to this call
+    net->time += iters;  // S:343, once per gradientStep
     if (net->trace) trace_dump(net, 3, 2);
     if (per_step_loss_or_null) {
         B2_CHECK_CUDA(cudaMemcpyAsync(per_step_loss_or_null, loss_dev, loss_bytes, cudaMemcpyDeviceToHost, net->stream));

@@ -208,6 +208,7 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
         } else {
             B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));  // host buffers are the caller's again
         }
+        net->time++;  // S:343
         return B2NN_OK;
     }
     B2_TRY(wide_ensure_batch(net, B));
@@ -221,6 +222,7 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
     B2_TRY(wide_output(net, B, true, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
     B2_TRY(wide_join(net));
+    net->time++;  // S:343
     if (mean_loss_or_null) {
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {
@@ -246,6 +248,7 @@ int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, co
     B2_TRY(wide_output(net, B, false, mean_loss_or_null ? net->wb.loss_sum : nullptr));
     B2_TRY(wide_backward(net, B, B * net->world, step, momentum));
     B2_TRY(wide_join(net));
+    net->time++;  // S:343
     if (mean_loss_or_null) {
         B2_TRY(read_mean_loss(net, net->wb.loss_sum, B, mean_loss_or_null));
     } else {

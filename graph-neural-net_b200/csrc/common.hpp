@@ -133,6 +133,7 @@ struct b2nn_net {
     int kind = 0, inner_act = 0, last_act = 0, loss = 0, precision = 0, flags = 0;
     double inner_param = 0, last_param = 0;
     int64_t n_weights = 0;
+    int64_t time = 0;  // gradient steps taken (`time`, S:23,343; the reference feeds it to the noise term only, Q12)
     std::vector<int64_t> w_off;
     cudaStream_t stream = nullptr;
     bool own_stream = false;

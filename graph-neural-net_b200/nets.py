@@ -142,6 +142,22 @@ class NeuralNet:
             raise ValueError("expected %d entries" % self.numWeights)
         capi.check(capi.lib().b2nn_set_velocity(self._h, _d(v)))
 
+    def getTime(self):
+        """`time` (S:23): gradient steps taken (S:343)."""
+        t = C.c_int64(0)
+        capi.check(capi.lib().b2nn_time(self._h, C.byref(t)))
+        return t.value
+
+    def saveCheckpoint(self, path):
+        """weights, previousUpdate and time to a flat file (csrc/checkpoint.cu); the reference has no persistence."""
+        import os
+        capi.check(capi.lib().b2nn_checkpoint_save(self._h, os.fsencode(path)))
+
+    def loadCheckpoint(self, path):
+        """restore what saveCheckpoint wrote; layerDims, class and functions must match (ValueError otherwise)."""
+        import os
+        capi.check(capi.lib().b2nn_checkpoint_load(self._h, os.fsencode(path)))
+
     def gradientStepLabeled(self, x, labels, step, momentum, returnLoss=False):
         """one-hot targets + narrow host dtypes (wide BF16 nets)."""
         x = np.ascontiguousarray(x)

@@ -145,6 +145,20 @@ int b2nn_set_weights(b2nn_net *net, const double *w_flat);
 int b2nn_get_velocity(b2nn_net *net, double *v_flat);
 int b2nn_set_velocity(b2nn_net *net, const double *v_flat);
 
+/* `time` (S:23): gradient steps taken by this net (S:343); restored by b2nn_checkpoint_load */
+int b2nn_time(const b2nn_net *net, int64_t *time);
+/* Checkpoint file (the reference has no persistence: a trained net is lost at process exit, and the 500 000-
+ * iteration run of logs/trainLog.csv:5 cannot be resumed).  Holds exactly what gradientStep mutates (S:327-344):
+ * weights, previousUpdate (velocity) and time, as FP64 in the boundary layout, plus the constructor arguments and a
+ * checksum; byte layout in graph-neural-net_b200/csrc/checkpoint.cu.  save writes path + ".tmp" and renames.
+ * load requires equal layerDims, net class and activation / loss functions (B2NN_ERR_DIM_MISMATCH otherwise; the
+ * precision may differ, so an FP64 run can be resumed in BF16 or TF32 and back) and leaves the net untouched when
+ * the file is damaged.  info reads the header only and needs no GPU; any out pointer may be NULL. */
+int b2nn_checkpoint_save(b2nn_net *net, const char *path);
+int b2nn_checkpoint_load(b2nn_net *net, const char *path);
+int b2nn_checkpoint_info(const char *path, int32_t *n_dims, int32_t *dims, int32_t dims_cap, int32_t *net_kind,
+                         int32_t *precision, int64_t *time, int64_t *n_weights);
+
 /* ---- trainer fast path (NeuralNetTrainer, T:28-92,143-168) --------------- */
 /* dataMaster (T:35-40): rows staged once.  Exactly one of t / labels may be
  * NULL: t is [n][dL] dense targets, labels [n] class ids (one-hot implied).
