@@ -133,7 +133,8 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
     GemmArgs ga = g;
     ga.tile_counter = net->dynamic_tiles ? net->tile_counter : nullptr;
-    ga.dbg = getenv("B2NN_GEMM_DBG") ? atoi(getenv("B2NN_GEMM_DBG")) : 0;  // debug, read per launch
+    static const int gemm_dbg = getenv("B2NN_GEMM_DBG") ? atoi(getenv("B2NN_GEMM_DBG")) : 0;  // bring-up aid
+    ga.dbg = gemm_dbg;
     static const bool want_stalls = getenv("B2NN_GEMM_STALLS") != nullptr;  // debug: where the role warps wait
     static unsigned int *stalls_dev = nullptr;
     if (want_stalls) {

@@ -1,4 +1,5 @@
-"""TF32 bring-up probe 2: sweep the source-format fields of the instruction descriptor on all-ones operands."""
+"""TF32 bring-up probe 2: sweep the source-format fields of the instruction descriptor on all-ones operands.
+B2NN_GEMM_DBG is read once per process now: run one process per format (B2NN_GEMM_DBG = 1 | fmt << 4)."""
 import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
