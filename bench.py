@@ -297,6 +297,11 @@ def run_b2nn(args):
         if tf32:
             # MEASURED_PEAKS.json holds no TF32 figure: the profiling recipe's nominal dense TF32 peak stands in
             pk = dict(pk, tflops=1100.0, src="nominal dense TF32 peak (B200_PROFILING.md); no measured TF32 peak on file")
+            tpk = os.path.join(ROOT, "profiles", "tf32_peaks.json")   # written by scratch/tf32_peak.py on the GPU box
+            if os.path.exists(tpk):
+                with open(tpk) as f:
+                    pk = dict(pk, tflops=float(json.load(f)["tf32_tflops_sustained"]),
+                              src="measured (profiles/tf32_peaks.json: torch.matmul fp32 allow_tf32 8192^3, sustained)")
         achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
