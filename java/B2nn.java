@@ -59,6 +59,11 @@ final class B2nn {
 	static final MethodHandle EVALUATE = h("b2nn_evaluate",
 			FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS));
 	static final MethodHandle SYNC = h("b2nn_sync", FunctionDescriptor.of(JAVA_INT, ADDRESS));
+	static final MethodHandle TIME = h("b2nn_time", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+	static final MethodHandle CHECKPOINT_SAVE = h("b2nn_checkpoint_save",
+			FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+	static final MethodHandle CHECKPOINT_LOAD = h("b2nn_checkpoint_load",
+			FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
 	static final MethodHandle LAST_ERROR = h("b2nn_last_error", FunctionDescriptor.of(ADDRESS));
 
 	private B2nn() {

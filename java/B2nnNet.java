@@ -135,6 +135,44 @@ abstract class B2nnNet implements NeuralNet {
 		return layerDims[layerDims.length - 1];
 	}
 
+	/**
+	 * Not in the reference (it has no persistence, NeuralNet.java:7-67): weights, previousUpdate and time
+	 * (SoftmaxCrossEntropyNeuralNet.java:327-344) to one flat file, so a long MNISTTrainer run can stop and resume.
+	 */
+	public void saveCheckpoint(String path) {
+		try (Arena a = Arena.ofConfined()) {
+			B2nn.check((int) B2nn.CHECKPOINT_SAVE.invokeExact(handle, a.allocateFrom(path)));
+		} catch (RuntimeException | Error e) {
+			throw e;
+		} catch (Throwable t) {
+			throw new IllegalStateException(t);
+		}
+	}
+
+	/** restores what saveCheckpoint wrote; IllegalArgumentException when layerDims, class or functions differ */
+	public void loadCheckpoint(String path) {
+		try (Arena a = Arena.ofConfined()) {
+			B2nn.check((int) B2nn.CHECKPOINT_LOAD.invokeExact(handle, a.allocateFrom(path)));
+		} catch (RuntimeException | Error e) {
+			throw e;
+		} catch (Throwable t) {
+			throw new IllegalStateException(t);
+		}
+	}
+
+	/** `time` (SoftmaxCrossEntropyNeuralNet.java:23): gradient steps taken */
+	public long getTime() {
+		try (Arena a = Arena.ofConfined()) {
+			MemorySegment steps = a.allocate(java.lang.foreign.ValueLayout.JAVA_LONG);
+			B2nn.check((int) B2nn.TIME.invokeExact(handle, steps));
+			return steps.get(java.lang.foreign.ValueLayout.JAVA_LONG, 0);
+		} catch (RuntimeException | Error e) {
+			throw e;
+		} catch (Throwable t) {
+			throw new IllegalStateException(t);
+		}
+	}
+
 	static int[] checkedDims(MemorySegment handle) throws Throwable {
 		try (Arena a = Arena.ofConfined()) {
 			MemorySegment in = a.allocate(JAVA_INT), out = a.allocate(JAVA_INT);
