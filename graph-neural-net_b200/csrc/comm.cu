@@ -79,9 +79,8 @@ int comm_unique_id(void *id128) {
 
 int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
     B2_REQUIRE(world >= 1 && rank >= 0 && rank < world, B2NN_ERR_INVALID_ARG, "bad rank/world %d/%d", rank, world);
-    B2_REQUIRE(net->precision == B2NN_PREC_BF16, B2NN_ERR_UNSUPPORTED,
-               "data-parallel training is implemented for the BF16 path only (tiny FP64 nets are replicas only; TF32 nets "
-               "are single-GPU: the fused exchange kernel replicates a BF16 operand copy they do not have)");
+    B2_REQUIRE(is_wide_precision(net->precision), B2NN_ERR_UNSUPPORTED,
+               "data-parallel training is implemented for the tensor-core path only (tiny FP64 nets are replicas only)");
     if (world == 1) { net->rank = 0; net->world = 1; return B2NN_OK; }
     NcclApi *a = nccl();
     B2_REQUIRE(a != nullptr, B2NN_ERR_NCCL, "NCCL library not found (set B2NN_NCCL_LIB)");
@@ -106,7 +105,9 @@ int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
 
 // ---- peer memory (CUDA IPC): lets the fused reduce/update kernel (dp_kernels.cuh) address every rank's arena ----
 int comm_ipc_export(b2nn_net *net, void *handle64) {
-    B2_REQUIRE(net->arena != nullptr, B2NN_ERR_UNSUPPORTED, "peer memory is for BF16 nets");
+    B2_REQUIRE(net->arena != nullptr && net->precision == B2NN_PREC_BF16, B2NN_ERR_UNSUPPORTED,
+               "the peer-memory exchange is for BF16 nets (its fused kernel replicates the BF16 operand copy); TF32 "
+               "nets use the NCCL all-reduce + update exchange");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
     B2_CHECK_CUDA(cudaIpcGetMemHandle(&h, net->arena));

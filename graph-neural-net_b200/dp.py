@@ -47,6 +47,11 @@ def init_comm(net, dist, rank=None, world=None):
     # 0.769 ms against 0.848 ms for plain peer memory), plain peer memory at 2 (there multimem sends the local
     # half through the switch as well: 0.799 against 0.768 ms).  profiles/r01_scaling.md has the runs.
     mode = os.environ.get("B2NN_DP") or ("nvls" if world >= 4 else "p2p")
+    from . import _capi as capi
+    if getattr(net, "precision", None) == capi.PREC_TF32:
+        # TF32 nets have no BF16 operand copy for the fused kernel to replicate: per-layer NCCL all-reduce of the
+        # FP32 gradient + the local update, every replica keeping its full FP32 master (= operand) array
+        mode = "nccl"
     if world > 1 and mode == "nvls":
         if _init_nvls(net, dist, rank, world):
             return rank, world

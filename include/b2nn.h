@@ -80,7 +80,8 @@ enum b2nn_precision {
     B2NN_PREC_F64 = 0,  /* parity mode: double everywhere, like the JVM */
     B2NN_PREC_BF16 = 1, /* tcgen05 kind::f16 GEMMs, FP32 accumulate, FP32 master W and V */
     B2NN_PREC_TF32 = 2  /* tcgen05 kind::tf32 GEMMs over FP32 activations / deltas / master weights (no operand
-                         * copy), FP32 accumulate; single GPU (b2nn_comm_init returns UNSUPPORTED) */
+                         * copy), FP32 accumulate; data-parallel through the NCCL exchange only (the peer-memory
+                         * and multicast exports return UNSUPPORTED) */
 };
 
 enum b2nn_flags {

@@ -124,8 +124,8 @@ def gloo_init_comm_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-def nccl_worker(rank, world, port, out_dir):
-    """BF16 nets, one per GPU, stepping on their slice of each global batch with the per-layer NCCL
+def nccl_worker(rank, world, port, out_dir, precision_name="bf16"):
+    """BF16 (or TF32) nets, one per GPU, stepping on their slice of each global batch with the per-layer NCCL
     all-reduce inside libb2nn.so; rank 0 also steps an un-sharded net on the whole global batch."""
     import torch
     import __graft_entry__ as ge
@@ -133,13 +133,14 @@ def nccl_worker(rank, world, port, out_dir):
     dist = _init(rank, world, port, "nccl")
     g = ge.load_package()
     dims, gB, iters, step, mu = [256, 384, 128, 40], 256 * world, 6, 0.05, 0.9
+    prec = g.capi.PREC_TF32 if precision_name == "tf32" else g.capi.PREC_BF16
     flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX
     rng = np.random.RandomState(11)
     n_rows = 4 * gB
     x = rng.rand(n_rows, dims[0]).astype(np.float32)
     lab = rng.randint(0, dims[-1], n_rows).astype(np.int32)
     idx = g.Sampler(n_rows, seed=1).draw(iters, gB)
-    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=prec,
                                          flags=flags, device=rank)
     g.dp.init_comm(net, dist)
     mine = g.dp.shard_index_lists(idx, rank, world)
@@ -154,7 +155,7 @@ def nccl_worker(rank, world, port, out_dir):
     flag = torch.tensor([1 if same else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
-        single = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+        single = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=prec,
                                                 flags=flags, device=0)
         w0 = single.getWeights()
         for it in range(iters):

@@ -210,9 +210,10 @@ def test_tf32_pixel_byte_rows_match_float_rows(g):
     assert da.evaluate()[0] == db.evaluate()[0]
 
 
-def test_tf32_data_parallel_is_refused(g):
-    """TF32 nets are single-GPU (the fused exchange kernel replicates a BF16 operand copy they do not have)"""
+def test_tf32_peer_memory_exchange_is_refused(g):
+    """TF32 nets exchange gradients through NCCL only: the fused peer-memory / multicast kernel replicates a BF16
+    operand copy they do not have (dp.init_comm picks the NCCL exchange for them)"""
     net = tf32_net(g, [64, 32, 8])
-    ident = (C.c_char * 128)()
     with pytest.raises(NotImplementedError):
-        g.capi.check(g.capi.lib().b2nn_comm_init(net._h, ident, 0, 2))
+        net.commIpcExport()
+    assert net.commNvlsExport() is None
