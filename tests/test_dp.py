@@ -90,20 +90,3 @@ def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
     assert str(r["mode"]) in ((mode, "p2p") if mode == "nvls" else (mode,))
     print("exchange:", str(r["mode"]))
 
-
-@pytest.mark.gpu
-def test_world2_tf32_matches_single_gpu(g, tmp_path, monkeypatch):
-    """TF32 nets shard the batch the same way; dp.init_comm gives them the NCCL all-reduce + local update exchange
-    whatever B2NN_DP says (they have no BF16 operand copy for the fused kernel to replicate).  Same bound as above."""
-    import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    import torch.multiprocessing as mp
-    from tests import dp_workers
-    monkeypatch.setenv("B2NN_DP", "p2p")
-    mp.spawn(dp_workers.nccl_worker, args=(2, _free_port(), str(tmp_path), "tf32"), nprocs=2, join=True)
-    r = np.load(tmp_path / "nccl.npz")
-    assert int(r["replicas_equal"]) == 1
-    du_dp, du_1 = r["w_dp"] - r["w0"], r["w_single"] - r["w0"]
-    assert np.linalg.norm(du_dp - du_1) / np.linalg.norm(du_1) < 2e-3
-    assert str(r["mode"]) == "nccl"
