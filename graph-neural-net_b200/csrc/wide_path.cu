@@ -607,14 +607,11 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
 
 // make the main stream wait for every update still running on the side stream
 int wide_join(b2nn_net *net) {
-    bool any = false;
     for (size_t l = 0; l < net->upd_pending.size(); l++)
         if (net->upd_pending[l]) {
             B2_CHECK_CUDA(cudaStreamWaitEvent(net->stream, net->upd_done[l], 0));
             net->upd_pending[l] = 0;
-            any = true;
         }
-    (void)any;
     return B2NN_OK;
 }
 
