@@ -61,6 +61,7 @@ def test_gloo_world2_init_comm_sequences(g, tmp_path):
         assert c[("nvls", True)][1:] == [("nvls_export",), ("nvls_import", pairs), ("nvls_team", team_arg),
                                          ("nvls_bind",)]
         assert c[("nvls", False)][1:] == [("nvls_export",), ("ipc_export",), ("ipc_import", [0, 1])]
+        assert c[("tf32", "p2p")] == c[("tf32", "nvls")] == [("init", b"u" * 128, r, 2)]   # TF32 nets: NCCL exchange only
         assert "rank(s) [1]" in c["failure"] and "999" in c["failure"]     # raised on both ranks, naming rank 1
 
 
