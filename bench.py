@@ -34,8 +34,14 @@ WORKLOADS = {
                     "(BASELINE configs[4])"),
     "c2": dict(dims=[784, 300, 100, 10], batch=16, prec="f64", step=0.0125,
                desc="784-300-100-10 Softmax/CE, batch 16, FP64 parity mode (BASELINE configs[1])"),
+    "c1": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01,
+               desc="784-100-50-10 SoftmaxCrossEntropyNeuralNet, batch 8, FP64 parity mode (BASELINE configs[0], "
+                    "logs/trainLog.csv:3)"),
+    "c3": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01, general=True,
+               desc="GeneralNeuralNet 784-100-50-10, sigmoid inner / outer, half squared error, batch 8, FP64 parity "
+                    "mode (BASELINE configs[2])"),
 }
-CPU_SAMPLE_ROWS = {"c4": 4, "c5": 2, "c2": 16}
+CPU_SAMPLE_ROWS = {"c4": 4, "c5": 2, "c2": 16, "c1": 8, "c3": 8}
 
 
 _REAL_STDOUT = None
@@ -148,8 +154,11 @@ def cpu_reference_run(workload, steps, warmup):
     from oracle import oracle as orc
     wl = WORKLOADS[workload]
     dims, rows = wl["dims"], CPU_SAMPLE_ROWS[workload]
-    net = orc.OracleNet(dims)
-    if workload != "c2":  # same fan-in-scaled init as the GPU arm so exp() stays finite
+    if wl.get("general"):
+        net = orc.OracleNet(dims, kind=orc.NET_GENERAL, inner_act="sigmoid", inner_param=0.0, last_act="sigmoid")
+    else:
+        net = orc.OracleNet(dims)
+    if wl["prec"] != "f64":  # same fan-in-scaled init as the GPU arm so exp() stays finite
         w = net.get_weights()
         off = 0
         for l in range(len(dims) - 1):
@@ -219,6 +228,9 @@ def run_b2nn(args):
                                                   precision=g.capi.PREC_TF32 if tf32 else g.capi.PREC_BF16,
                                                   flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX,
                                                   device=local_rank)
+        if wl.get("general"):
+            return g.GeneralNeuralNet(dims, g.SIGMOID, g.SIGMOID_PRIME, g.SIGMOID, g.SIGMOID_PRIME,
+                                      g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, device=local_rank)
         return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
 
     net = make_net()
@@ -367,7 +379,7 @@ def run_b2nn(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cs, cw = {"c4": (10, 1), "c5": (3, 1), "c2": (500, 20)}[args.workload]   # ~10-15 s of CPU work each
+        cs, cw = {"c4": (10, 1), "c5": (3, 1), "c2": (500, 20), "c1": (3000, 50), "c3": (1500, 50)}[args.workload]   # ~10-15 s of CPU work each
         val, dt, r = cpu_reference_run(args.workload, cs, cw)
         cpu = {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
                "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" %
@@ -384,7 +396,8 @@ def run_b2nn(args):
                        "exchange": net.commMode() if bf16 else "single",
                        "l2": "no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh "
                              "batch, larger than the 126 MB L2" % (n_weights(dims) * 12 / 1e6) if bf16 else
-                             "state is L2-resident by design (4.3 MB); batches cycle through 60000 rows (376 MB)"},
+                             "state is L2-resident by design (%.1f MB of weights + velocity); batches cycle through "
+                             "60000 rows (376 MB)" % (n_weights(dims) * 16 / 1e6)},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
             "clocks": sampler_thread.summary(),
         }
