@@ -234,7 +234,7 @@ def run_b2nn(args):
         return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
 
     net = make_net()
-    if world > 1:
+    if world > 1 and bf16:   # the tiny FP64 configs do not shard: N independent replicas, no exchange
         try:
             g.dp.init_comm(net, dist, rank, world)
         except RuntimeError as e:
@@ -392,7 +392,8 @@ def run_b2nn(args):
             "dtype": prec_name, "data": "synthetic",
             "config": {"workload": args.workload + ": " + (wl["desc"].replace("BF16", "TF32") if tf32 else wl["desc"]),
                        "dims": dims, "batch_per_gpu": B,
-                       "global_batch": B * world, "parallelism": "dp%d" % world,
+                       "global_batch": B * world,
+                       "parallelism": "dp%d" % world if bf16 else "replicas only x%d (no exchange)" % world,
                        "exchange": net.commMode() if bf16 else "single",
                        "l2": "no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh "
                              "batch, larger than the 126 MB L2" % (n_weights(dims) * 12 / 1e6) if bf16 else
