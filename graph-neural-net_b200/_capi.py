@@ -62,6 +62,8 @@ SIGNATURES = {
     "b2nn_kernel_launches": (C.c_int, [_vp, _lp]),
     "b2nn_profile_enable": (C.c_int, [_vp, C.c_int32]),
     "b2nn_profile_read": (C.c_int, [_vp, _dp, _lp, _dp]),
+    "b2nn_profile_read_classes": (C.c_int, [_vp, _dp, _lp]),
+    "b2nn_k1_profile": (C.c_int, [_vp, C.c_int32, _dp, _ip]),
     "b2nn_device_count": (C.c_int, [_ip]),
     "b2nn_version": (C.c_int, []),
     "b2nn_last_error": (C.c_char_p, []),

@@ -85,6 +85,7 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
         net->trace = getenv("B2NN_TRACE") != nullptr;
         net->dp_ctas = prop.multiProcessorCount;  // one 128-thread CTA per SM beside the GEMM (measured best at 8 GPUs)
         if (const char *dc = getenv("B2NN_DP_CTAS")) { if (atoi(dc) > 0) net->dp_ctas = atoi(dc); }
+        if (const char *to = getenv("B2NN_DP_TIMEOUT_MS")) { if (atof(to) > 0) net->dp_timeout_ns = (unsigned long long)(atof(to) * 1e6); }
         const char *dt = getenv("B2NN_DYNAMIC_TILES");
         net->dynamic_tiles = dt != nullptr && dt[0] == '1';
         net->dynamic_tiles_forced = dt != nullptr;
@@ -188,7 +189,7 @@ int b2nn_sync(b2nn_net *net) {
     B2_CHECK_CUDA(cudaSetDevice(net->device));
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     if (net->aux_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->aux_stream));
-    return B2NN_OK;
+    return check_device_error_words(net);
 }
 
 int b2nn_set_stream(b2nn_net *net, void *cuda_stream) {
@@ -212,11 +213,13 @@ int b2nn_profile_enable(b2nn_net *net, int32_t on) {
     B2_CHECK_CUDA(cudaSetDevice(net->device));
     if (on && net->prof_events.empty()) {
         net->prof_events.resize(4096);
+        net->prof_cls.assign(2048, 0);
         for (auto &e : net->prof_events) B2_CHECK_CUDA(cudaEventCreate(&e));
     }
     B2_TRY(profile_flush(net));
     net->profiling = on != 0;
     net->prof_flops = 0; net->prof_ms_acc = 0; net->prof_launch_acc = 0;
+    for (int c = 0; c < 4; c++) { net->prof_ms_cls[c] = 0; net->prof_n_cls[c] = 0; }
     return B2NN_OK;
 }
 
@@ -227,6 +230,25 @@ int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, do
     if (gemm_ms) *gemm_ms = net->prof_ms_acc;
     if (gemm_launches) *gemm_launches = net->prof_launch_acc;
     if (gemm_flops) *gemm_flops = net->prof_flops;
+    return B2NN_OK;
+}
+
+int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    B2_TRY(profile_flush(net));
+    for (int c = 0; c < 4; c++) {
+        if (ms4) ms4[c] = net->prof_ms_cls[c];
+        if (launches4) launches4[c] = net->prof_n_cls[c];
+    }
+    return B2NN_OK;
+}
+
+int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t *steps_or_null) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    if (cycles16_or_null) memcpy(cycles16_or_null, net->k1_prof_cycles, sizeof net->k1_prof_cycles);
+    if (steps_or_null) *steps_or_null = net->k1_prof_iters;
+    net->k1_prof = on != 0;
     return B2NN_OK;
 }
 

@@ -75,38 +75,18 @@ int b2nn_propagate(b2nn_net *net, const double *x, int32_t n, double *y) {
         }
         return B2NN_OK;
     }
-    // BF16: logits come back as FP32; softmax / last activation applied on the host in double
+    // tensor-core nets: FP32 logits -> softmax (S:197, S:357-376) / last activation (G:214-218) on the device, in double
     const int chunk = wide_eval_batch_rows(net);
     B2_TRY(wide_ensure_batch(net, chunk));
-    std::vector<float> z((size_t)chunk * pad8(dL));
+    B2_TRY(ensure_dscratch(net, (size_t)chunk * dL * sizeof(double)));
     for (int r0 = 0; r0 < n; r0 += chunk) {
         const int rows = (n - r0 < chunk) ? n - r0 : chunk;
         B2_TRY(wide_rows_from_host(net, x + (size_t)r0 * d0, B2NN_DT_F64, rows));
         B2_TRY(wide_forward(net, chunk));
-        B2_CHECK_CUDA(cudaMemcpyAsync(z.data(), net->wb.logits, (size_t)rows * pad8(dL) * sizeof(float),
+        B2_TRY(wide_propagate_rows(net, rows, (double *)net->dscratch));
+        B2_CHECK_CUDA(cudaMemcpyAsync(y + (size_t)r0 * dL, net->dscratch, (size_t)rows * dL * sizeof(double),
                                       cudaMemcpyDeviceToHost, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
-        for (int r = 0; r < rows; r++) {
-            const float *zr = z.data() + (size_t)r * pad8(dL);
-            double *yr = y + (size_t)(r0 + r) * dL;
-            if (net->kind == B2NN_NET_SOFTMAX_CE) {
-                double mx = zr[0], sum = 0;
-                for (int i = 1; i < dL; i++) mx = zr[i] > mx ? zr[i] : mx;
-                for (int i = 0; i < dL; i++) { yr[i] = exp((double)zr[i] - mx); sum += yr[i]; }
-                for (int i = 0; i < dL; i++) yr[i] /= sum;
-            } else {
-                for (int i = 0; i < dL; i++) {
-                    const double v = zr[i];
-                    switch (net->last_act) {
-                    case B2NN_ACT_LEAKY_RELU: yr[i] = v > 0 ? v : net->last_param * v; break;
-                    case B2NN_ACT_SIGMOID: yr[i] = 1.0 / (1.0 + exp(-v)); break;
-                    case B2NN_ACT_RELU: yr[i] = v > 0 ? v : 0.0; break;
-                    case B2NN_ACT_TANH: yr[i] = tanh(v); break;
-                    default: yr[i] = v;
-                    }
-                }
-            }
-        }
     }
     return B2NN_OK;
 }
@@ -194,6 +174,23 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
     if (net->precision == B2NN_PREC_F64) {
         B2_TRY(f64_ensure_work(net, B));
         B2_TRY(ensure_dscratch(net, 2 * sizeof(double)));
+        if (f64_fused_supported(net, B)) {
+            // the reference's per-step call (T:70, T:89) on the nets K1 serves: the batch is staged as a B-row data set
+            // and K1 runs ONE step over rows 0..B-1 -- one launch instead of a dozen, same arithmetic as the fast path
+            const int d0 = net->dims[0];
+            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.xin, x, (size_t)B * d0 * sizeof(double), cudaMemcpyHostToDevice, net->stream));
+            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.t, t, (size_t)B * dL * sizeof(double), cudaMemcpyHostToDevice, net->stream));
+            B2_TRY(f64_iota(net, B));
+            double *loss_dev = mean_loss_or_null ? (double *)net->dscratch : nullptr;
+            B2_TRY(f64_fused_train(net, net->fw.xin, nullptr, net->fw.t, nullptr, net->fw.idx, 1, B, step, momentum, loss_dev));
+            if (mean_loss_or_null) {
+                B2_TRY(read_mean_loss(net, loss_dev, B, mean_loss_or_null));
+            } else {
+                B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));  // host buffers are the caller's again
+            }
+            net->time++;  // S:343
+            return B2NN_OK;
+        }
         B2_TRY(f64_rows_from_host(net, x, B));
         B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.t, t, (size_t)B * dL * sizeof(double), cudaMemcpyHostToDevice,
                                       net->stream));

@@ -7,6 +7,7 @@
 
 #include <cstring>
 
+
 namespace b2nn {
 
 namespace {
@@ -105,9 +106,10 @@ int comm_init(b2nn_net *net, const void *id128, int rank, int world) {
 
 // ---- peer memory (CUDA IPC): lets the fused reduce/update kernel (dp_kernels.cuh) address every rank's arena ----
 int comm_ipc_export(b2nn_net *net, void *handle64) {
-    B2_REQUIRE(net->arena != nullptr && net->precision == B2NN_PREC_BF16, B2NN_ERR_UNSUPPORTED,
-               "the peer-memory exchange is for BF16 nets (its fused kernel replicates the BF16 operand copy); TF32 "
-               "nets use the NCCL all-reduce + update exchange");
+    B2_REQUIRE(net->arena != nullptr && is_wide_precision(net->precision), B2NN_ERR_UNSUPPORTED,
+               "the peer-memory exchange is for the tensor-core (BF16 / TF32) nets");
+    B2_REQUIRE(net->n_dims - 1 <= DP_MAX_LAYERS, B2NN_ERR_UNSUPPORTED,
+               "the peer-memory exchange supports up to %d weight matrices (flag block layout)", DP_MAX_LAYERS);
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaIpcMemHandle_t h;
     B2_CHECK_CUDA(cudaIpcGetMemHandle(&h, net->arena));
@@ -118,7 +120,8 @@ int comm_ipc_export(b2nn_net *net, void *handle64) {
 int comm_ipc_import(b2nn_net *net, const void *handles, int world) {
     B2_REQUIRE(world == net->world && world <= DP_MAX_WORLD, B2NN_ERR_INVALID_ARG,
                "world %d does not match the communicator (%d) or exceeds %d", world, net->world, DP_MAX_WORLD);
-    B2_REQUIRE(net->n_dims - 1 <= 32, B2NN_ERR_UNSUPPORTED, "peer-memory path supports up to 32 weight matrices");
+    B2_REQUIRE(net->n_dims - 1 <= DP_MAX_LAYERS, B2NN_ERR_UNSUPPORTED,
+               "the peer-memory exchange supports up to %d weight matrices (flag block layout)", DP_MAX_LAYERS);
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     net->peer_arena.assign(world, nullptr);
     for (int p = 0; p < world; p++) {

@@ -122,8 +122,11 @@ int steal_fd(int pid, int fd) {
 int comm_vmm_export(b2nn_net *net, int32_t *pid, int32_t *fd) {
     Drv *d = driver();
     B2_REQUIRE(d != nullptr, B2NN_ERR_UNSUPPORTED, "CUDA virtual-memory / multicast driver entry points not available");
-    B2_REQUIRE(net->arena != nullptr && net->precision == B2NN_PREC_BF16 && net->world > 1, B2NN_ERR_UNSUPPORTED,
-               "needs a BF16 net with a communicator (TF32 nets use the NCCL all-reduce + update exchange)");
+    B2_REQUIRE(net->arena != nullptr && is_wide_precision(net->precision) && net->world > 1, B2NN_ERR_UNSUPPORTED,
+               "needs a tensor-core (BF16 / TF32) net with a communicator");
+    // before the arena moves: the flag block at its head holds DP_MAX_LAYERS rows per handshake array
+    B2_REQUIRE(net->n_dims - 1 <= DP_MAX_LAYERS, B2NN_ERR_UNSUPPORTED,
+               "the in-switch exchange supports up to %d weight matrices (flag block layout)", DP_MAX_LAYERS);
     B2_REQUIRE(!net->vmm_arena, B2NN_ERR_INVALID_ARG, "arena already exported");
     B2_REQUIRE(net->peer_arena.empty(), B2NN_ERR_INVALID_ARG, "the arena is already shared through CUDA IPC");
     {

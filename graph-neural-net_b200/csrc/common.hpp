@@ -68,6 +68,8 @@ inline int pad8(int x) { return x >= 64 ? (x + 63) & ~63 : (x + 7) & ~7; }
 inline bool is_wide_precision(int precision) { return precision == B2NN_PREC_BF16 || precision == B2NN_PREC_TF32; }
 constexpr size_t DP_FLAG_BYTES = 8192;  // head of the arena: cross-GPU flags of the fused reduce/update kernel
 constexpr int DP_MAX_WORLD = 8;
+constexpr int DP_MAX_LAYERS = 32;   // weight matrices the flag block has handshake rows for (dp_kernels.cuh)
+constexpr int kMaxDevices = 64;     // per-device bookkeeping of function attributes (one process may drive several GPUs)
 
 
 // ---- per-layer state ----------------------------------------------------------------------
@@ -159,8 +161,12 @@ struct b2nn_net {
     struct Fused {
         double *V0t = nullptr, *V1b = nullptr, *V2r = nullptr, *z1buf = nullptr, *z2buf = nullptr;
         unsigned long long *bar = nullptr;
+        unsigned long long *prof = nullptr;  // [16] phase cycle sums of CTA 0 (b2nn_k1_profile / B2NN_K1_PROF)
         int cap_B = 0;
     } fused;
+    bool k1_prof = false;            // collect K1's phase counters (b2nn_k1_profile)
+    double k1_prof_cycles[16] = {};  // ... of the last K1 launch, cycles per step
+    int k1_prof_iters = 0;
     bool fused_f64_disabled = false;  // B2NN_F64_FUSED=0 forces the general multi-kernel path
     bool coop_launch = false;
     int max_smem_optin = 0;
@@ -189,6 +195,7 @@ struct b2nn_net {
     char *mc_base = nullptr;         // multicast mapping of all ranks' arenas (multimem.* addresses)
     std::vector<CUmemGenericAllocationHandle> peer_handles;
     unsigned int dp_seq = 0;         // sequence number of the cross-GPU flag handshakes
+    unsigned long long dp_timeout_ns = 20ull * 1000000000ull;  // bound of every cross-GPU wait (B2NN_DP_TIMEOUT_MS)
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;
     std::vector<cudaEvent_t> layer_events;
@@ -200,13 +207,17 @@ struct b2nn_net {
     bool trace = false;
     std::vector<std::pair<cudaEvent_t, std::string>> trace_marks;
 
-    // profiling (b2nn_profile_enable): event pairs around GEMM launches
+    // profiling (b2nn_profile_enable): event pairs around the launches of the tensor-core path, by kernel class
+    // (0 contraction, 1 momentum update / exchange, 2 output delta, 3 input prologue + label gather)
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
+    std::vector<unsigned char> prof_cls;   // class of pair i (events 2i, 2i+1)
     size_t prof_used = 0;
     double prof_flops = 0;
-    double prof_ms_acc = 0;
-    int64_t prof_launch_acc = 0;
+    double prof_ms_acc = 0;         // class 0
+    int64_t prof_launch_acc = 0;    // class 0
+    double prof_ms_cls[4] = {0, 0, 0, 0};
+    int64_t prof_n_cls[4] = {0, 0, 0, 0};
 
     // host staging
     void *pinned = nullptr;

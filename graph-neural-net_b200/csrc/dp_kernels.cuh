@@ -13,6 +13,10 @@
 //   3. handshake: "my slice is written everywhere"; the kernel ends when all peers said so, i.e. when this
 //      rank's wn is complete and its gradient buffer is no longer being read.
 // Wire traffic per parameter: (G-1)/G x (4 B in + 2 B out); the gradient never makes a second trip through HBM.
+// TF32 nets have no BF16 operand copy -- their GEMMs read the FP32 master array itself -- so for them the owner
+// replicates the updated FP32 weights (4 B out instead of 2); the velocity stays sharded either way.
+// Every cross-GPU wait is bounded (Args::timeout_ns, %globaltimer): a peer that never arrives sets Flags::error,
+// the kernel skips its work and ends, and the host turns the word into B2NN_ERR_CUDA at the next synchronising call.
 #pragma once
 #include <cuda_bf16.h>
 
@@ -24,7 +28,7 @@
 namespace b2nn {
 namespace dp {
 
-constexpr int MAX_LAYERS = 32;
+constexpr int MAX_LAYERS = DP_MAX_LAYERS;
 // Small CTAs on purpose: the kernel runs BESIDE the persistent GEMM (320 threads x up to 128 registers = 41 K of
 // the SM's 64 K registers); 128 threads x <= 96 registers fit next to it, a 256 x 172 CTA did not and the two
 // kernels time-shared the SMs (measured at 8 GPUs: the next forward GEMM took 2.6x longer).
@@ -35,7 +39,11 @@ struct Flags {
     unsigned int done[MAX_LAYERS][DP_MAX_WORLD];   // [l][p]: rank p has written its slice of layer l everywhere
     unsigned int go[MAX_LAYERS];                   // local: CTA 0 saw every peer's ready flag
     unsigned int finished[MAX_LAYERS];             // local: CTAs of this launch that finished their part
+    unsigned int error;                            // local, sticky: 0, or DP_ERR_* | layer << 8 | peer of the wait that timed out
 };
+constexpr unsigned int DP_ERR_READY = 0x01000000u;  // a peer's gradient never became ready
+constexpr unsigned int DP_ERR_DONE = 0x02000000u;   // a peer never reported its slice written
+constexpr unsigned int DP_ERR_GO = 0x03000000u;     // CTA 0 of this launch never released the others
 static_assert(sizeof(Flags) <= DP_FLAG_BYTES, "flag block does not fit");
 
 struct Args {
@@ -46,6 +54,8 @@ struct Args {
     long long n4;               // float4 elements of the layer (padded [in][ld_n] array)
     float scale, momentum;
     unsigned int seq;           // handshake sequence number, identical on all ranks for this launch
+    int f32_operand;            // TF32 nets: replicate the FP32 weights themselves (no BF16 copy exists)
+    unsigned long long timeout_ns;  // bound of every cross-GPU wait
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
@@ -71,6 +81,25 @@ __device__ __forceinline__ float4 multimem_ld_reduce_add(const void *mc_addr) {
                  : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// spin until *p == want (acquire at system scope); false when `timeout_ns` passed first
+__device__ __forceinline__ bool wait_flag_sys(const unsigned int *p, unsigned int want, unsigned long long timeout_ns) {
+    if (ld_acquire_sys(p) == want) return true;
+    const unsigned long long t0 = globaltimer_ns();
+    while (ld_acquire_sys(p) != want)
+        if (globaltimer_ns() - t0 > timeout_ns) return false;
+    return true;
+}
+// 16 bytes (four FP32) replicated into every GPU of the team by the switch
+__device__ __forceinline__ void multimem_st_f32x4(void *mc_addr, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
 // 8 bytes (four BF16) replicated into every GPU of the team by the switch
 __device__ __forceinline__ void multimem_st_bf16x4(void *mc_addr, uint2 b) {
     asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc_addr), "r"(b.x), "r"(b.y) : "memory");
@@ -86,8 +115,8 @@ reduce_update_kernel(const Args a) {
             Flags *peer = reinterpret_cast<Flags *>(a.arena[threadIdx.x]);
             __threadfence_system();
             st_release_sys(&peer->ready[l][a.rank], a.seq);
-            while (ld_acquire_sys(&mine->ready[l][threadIdx.x]) != a.seq) {
-            }
+            if (!wait_flag_sys(&mine->ready[l][threadIdx.x], a.seq, a.timeout_ns))
+                atomicCAS(&mine->error, 0u, DP_ERR_READY | ((unsigned)l << 8) | threadIdx.x);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -95,11 +124,18 @@ reduce_update_kernel(const Args a) {
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&mine->go[l]), "r"(a.seq) : "memory");
         }
     } else {
-        if (threadIdx.x == 0)
-            while (ld_acquire_gpu(&mine->go[l]) != a.seq) {
-            }
+        if (threadIdx.x == 0 && ld_acquire_gpu(&mine->go[l]) != a.seq) {
+            const unsigned long long t0 = globaltimer_ns();
+            while (ld_acquire_gpu(&mine->go[l]) != a.seq)
+                if (globaltimer_ns() - t0 > 2 * a.timeout_ns) {
+                    atomicCAS(&mine->error, 0u, DP_ERR_GO | ((unsigned)l << 8));
+                    break;
+                }
+        }
         __syncthreads();
     }
+    // a wait above (in this or an earlier launch) timed out: a peer is gone.  Touch nothing, fall through to the end.
+    const bool aborted = ld_acquire_gpu(&mine->error) != 0u;
 
     // ---- 2. owned slice: reduce over the peers, update, broadcast the BF16 copy ----
     const long long lo = (long long)a.rank * a.n4 / a.world, hi = (long long)(a.rank + 1) * a.n4 / a.world;
@@ -108,7 +144,7 @@ reduce_update_kernel(const Args a) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     // NVLink reads are latency-bound per request: keep UNROLL x world 16-byte loads in flight per thread
     constexpr int UNROLL = 4;
-    for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += stride * UNROLL) {
+    for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi && !aborted; q0 += stride * UNROLL) {
         float4 g[UNROLL], wv[UNROLL], vv[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -149,6 +185,17 @@ reduce_update_kernel(const Args a) {
             V.z = a.scale * g[u].z + a.momentum * V.z; V.w = a.scale * g[u].w + a.momentum * V.w;
             W.x -= V.x; W.y -= V.y; W.z -= V.z; W.w -= V.w;
             v[q] = V;
+            if (a.f32_operand) {
+                // TF32 net: every rank's GEMMs read the FP32 array itself -- replicate it (own copy included)
+                if (a.mc != nullptr) {
+                    multimem_st_f32x4(reinterpret_cast<float4 *>(a.mc + a.off_w) + q, W);
+                } else {
+#pragma unroll
+                    for (int p = 0; p < DP_MAX_WORLD; p++)
+                        if (p < a.world) __stcg(reinterpret_cast<float4 *>(a.arena[p] + a.off_w) + q, W);
+                }
+                continue;
+            }
             w[q] = W;
             const uint2 b = make_uint2(pack_bf16x2(W.x, W.y), pack_bf16x2(W.z, W.w));
             if (a.mc != nullptr) {
@@ -169,12 +216,12 @@ reduce_update_kernel(const Args a) {
     __syncthreads();
     if (last) {
         if (threadIdx.x == 0) mine->finished[l] = 0u;
-        if ((int)threadIdx.x < a.world) {
+        if ((int)threadIdx.x < a.world && ld_acquire_gpu(&mine->error) == 0u) {
             Flags *peer = reinterpret_cast<Flags *>(a.arena[threadIdx.x]);
             __threadfence_system();
             st_release_sys(&peer->done[l][a.rank], a.seq);
-            while (ld_acquire_sys(&mine->done[l][threadIdx.x]) != a.seq) {
-            }
+            if (!wait_flag_sys(&mine->done[l][threadIdx.x], a.seq, a.timeout_ns))
+                atomicCAS(&mine->error, 0u, DP_ERR_DONE | ((unsigned)l << 8) | threadIdx.x);
         }
     }
 }

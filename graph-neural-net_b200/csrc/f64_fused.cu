@@ -90,7 +90,8 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
         B2_CHECK_CUDA(cudaMalloc(&fs.V0t, (size_t)d1 * d0 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.V1b, (size_t)d1 * d2 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.V2r, (size_t)G * d2 * d3 * sizeof(double)));
-        B2_CHECK_CUDA(cudaMalloc(&fs.bar, sizeof(unsigned long long)));
+        B2_CHECK_CUDA(cudaMalloc(&fs.bar, 2 * sizeof(unsigned long long)));
+        B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, 2 * sizeof(unsigned long long), net->stream));
         B2_CHECK_CUDA(cudaFuncSetAttribute(fused_kernel_for(net->inner_act),
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, net->max_smem_optin));
     }
@@ -107,8 +108,8 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     p.bulk = Xu8 ? (d0 % 16 == 0) : (d0 % 2 == 0);
     if (getenv("B2NN_F64_NO_BULK")) p.bulk = 0;
     B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, sizeof(unsigned long long), net->stream));
-    static unsigned long long *prof_dev = nullptr;
-    const bool prof = getenv("B2NN_K1_PROF") != nullptr;
+    unsigned long long *&prof_dev = fs.prof;   // per net (hence per device)
+    const bool prof = getenv("B2NN_K1_PROF") != nullptr || net->k1_prof;
     if (prof) {
         if (!prof_dev) B2_CHECK_CUDA(cudaMalloc(&prof_dev, 16 * sizeof(unsigned long long)));
         B2_CHECK_CUDA(cudaMemsetAsync(prof_dev, 0, 16 * sizeof(unsigned long long), net->stream));
@@ -126,16 +127,20 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
         // W1 rows; slot 7 = W2)
         const char *names[16] = {"stage", "phase1", "barrier1", "phase2", "barrier2", "p3:delta2", "phase4", "p5:W2",
                                  "p3:a2", "p3:z3", "p3:softmax", "p3:loss", "p5:W0", "p5:W1c", "p5:W1r", "stage:wait"};
-        fprintf(stderr, "[b2nn K1 prof] cycles per step (CTA 0):");
-        for (int i = 0; i < 16; i++) fprintf(stderr, " %s %.0f", names[i], (double)h[i] / iters);
-        fprintf(stderr, "\n");
+        for (int i = 0; i < 16; i++) net->k1_prof_cycles[i] = (double)h[i] / iters;
+        net->k1_prof_iters = iters;
+        if (getenv("B2NN_K1_PROF") != nullptr) {
+            fprintf(stderr, "[b2nn K1 prof] cycles per step (CTA 0):");
+            for (int i = 0; i < 16; i++) fprintf(stderr, " %s %.0f", names[i], (double)h[i] / iters);
+            fprintf(stderr, "\n");
+        }
     }
     return B2NN_OK;
 }
 
 void f64_fused_free(b2nn_net *net) {
     auto &fs = net->fused;
-    cudaFree(fs.V0t); cudaFree(fs.V1b); cudaFree(fs.V2r); cudaFree(fs.z1buf); cudaFree(fs.z2buf); cudaFree(fs.bar);
+    cudaFree(fs.V0t); cudaFree(fs.V1b); cudaFree(fs.V2r); cudaFree(fs.z1buf); cudaFree(fs.z2buf); cudaFree(fs.bar); cudaFree(fs.prof);
     fs = {};
 }
 

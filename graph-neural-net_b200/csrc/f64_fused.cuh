@@ -37,7 +37,7 @@ struct FusedParams {
     double *V2r;            // [grid][d2*d3] scratch: per-CTA velocity replica of W2
     double *z1buf;          // [2][B][d1] published pre-activations (double buffered by step parity)
     double *z2buf;          // [2][B][d2]
-    unsigned long long *bar;  // grid barrier counter (zeroed before launch)
+    unsigned long long *bar;  // [2]: grid barrier counter (zeroed before launch); sticky give-up word
     double *loss_out;       // [iters] sum over the batch of per-sample losses, or null
     // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
     int nc0max, nc1max;
@@ -56,15 +56,29 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
-__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target) {
+// Wait (thread 0) until the barrier counter reaches `target`.  Bounded: a cooperative launch keeps every CTA resident, so
+// the only way to wait forever is a CTA that died; after K1_MAX_POLLS polls (each an L2 round trip: seconds in total)
+// the CTA records the fact in bar[1] (the host turns it into B2NN_ERR_CUDA), stops waiting for good and lets the launch end.
+constexpr unsigned int K1_MAX_POLLS = 1u << 24;
+__device__ __forceinline__ void grid_barrier_wait(unsigned long long *bar, unsigned long long target, bool &gave_up) {
+    if (gave_up) return;
+    unsigned long long v;
+    unsigned int polls = 0;
+    do {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+    } while (v < target && ++polls < K1_MAX_POLLS);
+    if (v < target) {
+        gave_up = true;
+        atomicMax(bar + 1, (unsigned long long)polls);
+    }
+}
+
+__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target, bool &gave_up) {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(bar, 1ULL);
-        unsigned long long v;
-        do {
-            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
-        } while (v < target);
+        grid_barrier_wait(bar, target, gave_up);
     }
     __syncthreads();
 }
@@ -72,19 +86,15 @@ __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned l
 // the same barrier with `work()` run by the whole CTA between this CTA's arrival and the wait for the others: thread 0
 // polls, every other warp is idle there anyway
 template <class F>
-__device__ __forceinline__ void grid_barrier_overlap(unsigned long long *bar, unsigned long long target, F work) {
+__device__ __forceinline__ void grid_barrier_overlap(unsigned long long *bar, unsigned long long target, bool &gave_up,
+                                                     F work) {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(bar, 1ULL);
     }
     work();
-    if (threadIdx.x == 0) {
-        unsigned long long v;
-        do {
-            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
-        } while (v < target);
-    }
+    if (threadIdx.x == 0) grid_barrier_wait(bar, target, gave_up);
     __syncthreads();
 }
 
@@ -260,6 +270,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     if (p.bulk && warp == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar, lane);
 
     unsigned long long bar_target = 0;
+    bool gave_up = false;  // thread 0: a grid-barrier wait ran out of polls (see grid_barrier_wait)
     unsigned long long *profs = reinterpret_cast<unsigned long long *>(sm + p.o_prof);
     if (p.prof != nullptr && c == 0 && tid == 0)
         for (int i = 0; i < 16; i++) profs[i] = 0ULL;
@@ -335,7 +346,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         bar_target += G;
         // the byte staging buffer has been free since the batch was staged: warp 1 requests the NEXT batch while
         // thread 0 waits for the other CTAs
-        grid_barrier_overlap(p.bar, bar_target, [&] {
+        grid_barrier_overlap(p.bar, bar_target, gave_up, [&] {
             if (p.bulk && u8 && warp == 1 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar, lane);
         });
         K1_MARK(2)  // barrier 1
@@ -368,7 +379,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(3)  // phase 2
         bar_target += G;
-        grid_barrier(p.bar, bar_target);
+        grid_barrier(p.bar, bar_target, gave_up);
         K1_MARK(4)  // barrier 2
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----

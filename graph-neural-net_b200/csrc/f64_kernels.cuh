@@ -185,6 +185,11 @@ static __global__ void output_rows(const double *Z, const double *T, int rows, i
     if (pred) pred[r] = best;
 }
 
+static __global__ void iota_rows(int32_t *idx, int rows) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < rows) idx[r] = r;
+}
+
 // sequential (row-order) sum of per-row losses and hit count; one thread -- tiny inputs
 static __global__ void reduce_rows(const double *loss, const int32_t *pred, const int32_t *labels, int rows,
                             double *loss_sum, long long *hits) {

@@ -169,6 +169,13 @@ int f64_gradients(b2nn_net *net, int rows, double step, double momentum, double 
     return B2NN_OK;
 }
 
+int f64_iota(b2nn_net *net, int rows) {
+    f64::iota_rows<<<(rows + 127) / 128, 128, 0, net->stream>>>(net->fw.idx, rows);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
 int f64_reduce(b2nn_net *net, int rows, const int32_t *labels_dev, double *loss_sum_dev, long long *hits_dev) {
     auto &fw = net->fw;
     f64::reduce_rows<<<1, 32, 0, net->stream>>>(loss_sum_dev ? fw.row_loss : nullptr, hits_dev ? fw.pred : nullptr,

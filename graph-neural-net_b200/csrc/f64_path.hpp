@@ -13,6 +13,7 @@ int f64_output(b2nn_net *net, int rows, bool have_targets, double *P, bool want_
                bool want_pred);
 int f64_deltas(b2nn_net *net, int rows);
 int f64_gradients(b2nn_net *net, int rows, double step, double momentum, double *grad_out);
+int f64_iota(b2nn_net *net, int rows);  // fw.idx = 0, 1, .., rows-1
 int f64_reduce(b2nn_net *net, int rows, const int32_t *labels_dev, double *loss_sum_dev, long long *hits_dev);
 }  // namespace b2nn
 

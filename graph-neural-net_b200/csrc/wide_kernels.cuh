@@ -301,8 +301,10 @@ output_delta(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ 
     }
 }
 
-// Evaluation row pass: one warp per row.  `>=` argmax so the LAST maximal index wins
-// (MNISTTrainer.java:166-168) and the per-row loss.
+// Evaluation row pass: one warp per row.  The reference compares the ACTIVATED outputs with `>=` starting from
+// index 0 (MNISTTrainer.java:164-168: `if (out[i] >= out[actual]) actual = i`), so the LAST maximal index wins, a NaN
+// entry never wins, and a NaN at index 0 pins the answer to 0.  Softmax is strictly monotone in z, so softmax nets
+// compare the logits; general nets compare f_last(z) (ReLU / saturating sigmoid and tanh outputs tie where z does not).
 __global__ void eval_rows(const float *__restrict__ Z, int ld_z, const int32_t *__restrict__ labels, int rows,
                           int dL, int kind, int last_act, float last_param, int32_t *__restrict__ pred,
                           float *__restrict__ row_loss) {
@@ -310,26 +312,34 @@ __global__ void eval_rows(const float *__restrict__ Z, int ld_z, const int32_t *
     const int lane = threadIdx.x & 31;
     if (row >= rows) return;
     const float *z = Z + (size_t)row * ld_z;
-    float best = -INFINITY;
+    float best = -INFINITY, zbest = -INFINITY;
     int besti = -1;
     for (int c = lane; c < dL; c += 32) {
-        const float v = z[c];  // softmax / monotone last activations preserve the order of z
-        if (v >= best) { best = v; besti = c; }
+        const float zc = z[c];
+        const float v = kind == 0 ? zc : act_apply(last_act, last_param, zc);
+        if (v >= best) { best = v; besti = c; }   // false for NaN
+        zbest = fmaxf(zbest, zc);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float ob = __shfl_xor_sync(0xffffffffu, best, o);
         const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
-        if (ob > best || (ob == best && oi > besti)) { best = ob; besti = oi; }
+        if (oi >= 0 && (besti < 0 || ob > best || (ob == best && oi > besti))) { best = ob; besti = oi; }
+        zbest = fmaxf(zbest, __shfl_xor_sync(0xffffffffu, zbest, o));
+    }
+    {
+        const float z0 = z[0];
+        const float v0 = kind == 0 ? z0 : act_apply(last_act, last_param, z0);
+        if (besti < 0 || v0 != v0) besti = 0;
     }
     float loss = 0.f;
     if (row_loss && labels) {
         const int lab = labels[row];
         if (kind == 0) {
             float sum = 0.f;
-            for (int c = lane; c < dL; c += 32) sum += __expf(z[c] - best);
+            for (int c = lane; c < dL; c += 32) sum += __expf(z[c] - zbest);
             sum = warp_sum(sum);
-            loss = -(z[lab] - best - __logf(sum));
+            loss = -(z[lab] - zbest - __logf(sum));
         } else {
             float acc = 0.f;
             for (int c = lane; c < dL; c += 32) {
@@ -342,6 +352,41 @@ __global__ void eval_rows(const float *__restrict__ Z, int ld_z, const int32_t *
     if (lane == 0) {
         if (pred) pred[row] = besti;
         if (row_loss) row_loss[row] = loss;
+    }
+}
+
+// NeuralNet.propagate (src/NeuralNet.java:16) output pass of the tensor-core path: the FP32 logits of `rows` rows ->
+// the net's output vector in double, on the device: softmax (S:357-376; max-subtracted, mathematically identical) or
+// the last activation (G:214-218).  One warp per row; exp / sum / divide in double like the reference.
+__global__ void propagate_rows(const float *__restrict__ Z, int ld_z, int rows, int dL, int kind, int last_act,
+                               double last_param, double *__restrict__ P) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float *z = Z + (size_t)row * ld_z;
+    double *p = P + (size_t)row * dL;
+    if (kind == 0) {
+        float mx = -INFINITY;
+        for (int c = lane; c < dL; c += 32) mx = fmaxf(mx, z[c]);
+        mx = warp_max(mx);
+        double sum = 0.0;
+        for (int c = lane; c < dL; c += 32) sum += exp((double)z[c] - (double)mx);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        for (int c = lane; c < dL; c += 32) p[c] = exp((double)z[c] - (double)mx) / sum;
+    } else {
+        for (int c = lane; c < dL; c += 32) {
+            const double v = (double)z[c];
+            double a;
+            switch (last_act) {
+            case ACT_LEAKY_RELU: a = v > 0 ? v : last_param * v; break;
+            case ACT_SIGMOID: a = 1.0 / (1.0 + exp(-v)); break;
+            case ACT_RELU: a = v > 0 ? v : 0.0; break;
+            case ACT_TANH: a = tanh(v); break;
+            default: a = v;
+            }
+            p[c] = a;
+        }
     }
 }
 

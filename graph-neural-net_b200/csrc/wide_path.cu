@@ -93,14 +93,34 @@ void trace_dump(b2nn_net *net, int first, int count) {
 int profile_flush(b2nn_net *net) {
     if (net->prof_used) {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        if (net->copy_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->copy_stream));
         for (size_t i = 0; i + 1 < net->prof_used; i += 2) {
             float ms = 0.f;
             B2_CHECK_CUDA(cudaEventElapsedTime(&ms, net->prof_events[i], net->prof_events[i + 1]));
-            net->prof_ms_acc += ms;
-            net->prof_launch_acc++;
+            const int cls = net->prof_cls[i / 2] & 3;
+            net->prof_ms_cls[cls] += ms;
+            net->prof_n_cls[cls]++;
+            if (cls == 0) { net->prof_ms_acc += ms; net->prof_launch_acc++; }
         }
         net->prof_used = 0;
     }
+    return B2NN_OK;
+}
+
+// event pair of class `cls` around whatever is launched on `st` between prof_begin and prof_end (profiling on only)
+struct ProfPair { cudaEvent_t e1 = nullptr; };
+static int prof_begin(b2nn_net *net, int cls, cudaStream_t st, ProfPair *pp) {
+    pp->e1 = nullptr;
+    if (!net->profiling) return B2NN_OK;
+    if (net->prof_used + 2 > net->prof_events.size()) B2_TRY(profile_flush(net));
+    net->prof_cls[net->prof_used / 2] = (unsigned char)cls;
+    cudaEvent_t e0 = net->prof_events[net->prof_used++];
+    pp->e1 = net->prof_events[net->prof_used++];
+    B2_CHECK_CUDA(cudaEventRecord(e0, st));
+    return B2NN_OK;
+}
+static int prof_end(cudaStream_t st, const ProfPair &pp) {
+    if (pp.e1) B2_CHECK_CUDA(cudaEventRecord(pp.e1, st));
     return B2NN_OK;
 }
 
@@ -116,18 +136,15 @@ static GemmKernel gemm_kernel() {
 template <int EPI, bool A_MN, bool B_MN, bool TF32>
 static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
     const GemmKernel kernel = gemm_kernel<EPI, A_MN, B_MN, TF32>();
-    static bool attr_done = false;
-    if (!attr_done) {
+    // function attributes are per DEVICE: one process may hold nets on several GPUs (b2nn_create's `device`)
+    static bool attr_done[kMaxDevices] = {};
+    B2_REQUIRE(net->device >= 0 && net->device < kMaxDevices, B2NN_ERR_INVALID_ARG, "device ordinal %d", net->device);
+    if (!attr_done[net->device]) {
         B2_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-        attr_done = true;
+        attr_done[net->device] = true;
     }
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (net->profiling) {
-        if (net->prof_used + 2 > net->prof_events.size()) B2_TRY(profile_flush(net));
-        e0 = net->prof_events[net->prof_used++];
-        e1 = net->prof_events[net->prof_used++];
-        B2_CHECK_CUDA(cudaEventRecord(e0, net->stream));
-    }
+    ProfPair pp;
+    B2_TRY(prof_begin(net, 0, net->stream, &pp));
     const int tiles = ((g.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((g.N + GEMM_BN - 1) / GEMM_BN);
     const int max_pairs = net->num_sms / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
@@ -136,7 +153,8 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
     static const int gemm_dbg = getenv("B2NN_GEMM_DBG") ? atoi(getenv("B2NN_GEMM_DBG")) : 0;  // bring-up aid
     ga.dbg = gemm_dbg;
     static const bool want_stalls = getenv("B2NN_GEMM_STALLS") != nullptr;  // debug: where the role warps wait
-    static unsigned int *stalls_dev = nullptr;
+    static unsigned int *stalls_by_dev[kMaxDevices] = {};
+    unsigned int *&stalls_dev = stalls_by_dev[net->device];
     if (want_stalls) {
         if (!stalls_dev) B2_CHECK_CUDA(cudaMalloc(&stalls_dev, 8 * 148 * 2 * sizeof(unsigned int)));
         B2_CHECK_CUDA(cudaMemsetAsync(stalls_dev, 0, 8 * 148 * 2 * sizeof(unsigned int), net->stream));
@@ -158,10 +176,8 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
                     EPI, g.M, g.N, g.K, s[3] / P, s[4] / P, s[1] / P, s[2] / P, s[0] / C, s[5] / C, s[6] / C,
                     s[6] / C / (s[4] / P));
     }
-    if (net->profiling) {
-        B2_CHECK_CUDA(cudaEventRecord(e1, net->stream));
-        net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
-    }
+    B2_TRY(prof_end(net->stream, pp));
+    if (net->profiling) net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -180,8 +196,11 @@ static int launch_update(b2nn_net *net, WideLayer &y, float scale, float momentu
     long long blocks = (n4 + 255) / 256;
     const long long cap = (long long)net->num_sms * 8;
     if (blocks > cap) blocks = cap;
+    ProfPair pp;
+    B2_TRY(prof_begin(net, 1, st, &pp));
     wide::sgd_update<<<(int)blocks, 256, 0, st>>>((const float4 *)y.g, (float4 *)y.w, (float4 *)y.v, n4, scale,
                                                   momentum, cast_only, (uint2 *)y.wn);
+    B2_TRY(prof_end(st, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -237,9 +256,10 @@ int wide_download_weights(b2nn_net *net, double *w_flat, bool velocity) {
 // that SM until it exits.  Every kernel that runs beside or between the GEMMs therefore asks for the
 // max-shared carve-out too, so the side-stream update / input prologue really overlap and no
 // reconfiguration drain happens at kernel boundaries.
-static int prefer_max_shared_carveout() {
-    static bool done = false;
-    if (done) return B2NN_OK;
+static int prefer_max_shared_carveout(int device) {
+    static bool done_dev[kMaxDevices] = {};   // per device, like every function attribute
+    B2_REQUIRE(device >= 0 && device < kMaxDevices, B2NN_ERR_INVALID_ARG, "device ordinal %d", device);
+    if (done_dev[device]) return B2NN_OK;
     const int c = cudaSharedmemCarveoutMaxShared;
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::sgd_update, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(dp::reduce_update_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, c));
@@ -260,13 +280,14 @@ static int prefer_max_shared_carveout() {
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_labels, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::gather_targets, cudaFuncAttributePreferredSharedMemoryCarveout, c));
     B2_CHECK_CUDA(cudaFuncSetAttribute(wide::eval_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
-    done = true;
+    B2_CHECK_CUDA(cudaFuncSetAttribute(wide::propagate_rows, cudaFuncAttributePreferredSharedMemoryCarveout, c));
+    done_dev[device] = true;
     return B2NN_OK;
 }
 
 int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
     const int L = net->n_dims - 1;
-    B2_TRY(prefer_max_shared_carveout());
+    B2_TRY(prefer_max_shared_carveout(net->device));
     net->wide.resize(L);
     // One arena holds the cross-GPU flags and every layer's g / wn / w / v at the same offsets on every rank,
     // so that a single CUDA IPC handle lets the peers of a data-parallel group address all of it (comm.cu).
@@ -454,6 +475,8 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     if (const char *e = getenv("B2NN_PROLOGUE_THREADS")) { thr = atoi(e); grid = net->num_sms * blocks_per_sm; }
     const float p = (float)net->inner_param;
     const int act = net->inner_act, ld = pad8(d0);
+    ProfPair pp;
+    B2_TRY(prof_begin(net, 3, st, &pp));
     if (is_tf32(net)) {  // FP32 operand rows
         float *a0 = (float *)b.a[0];
         switch (x_dtype) {
@@ -487,6 +510,7 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
     }
     }
+    B2_TRY(prof_end(st, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -521,6 +545,8 @@ int wide_forward(b2nn_net *net, int B) {
 int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev) {
     WideBatch &b = net->wb;
     const int L = net->n_dims - 1, dL = net->dims[L], ldL = pad8(dL);
+    ProfPair pp;
+    B2_TRY(prof_begin(net, 2, net->stream, &pp));
     if (is_tf32(net))
         wide::output_delta<float><<<(B + 7) / 8, 256, 0, net->stream>>>(
             b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
@@ -531,6 +557,7 @@ int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev)
             b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
             net->last_act, (float)net->last_param, (__nv_bfloat16 *)b.d[L], ldL, b.row_loss, loss_slot_dev,
             b.block_partial, b.block_counter);
+    B2_TRY(prof_end(net->stream, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -582,14 +609,20 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
         a.mc = net->use_multimem ? net->mc_base : nullptr;
         a.world = net->world; a.rank = net->rank; a.layer = l;
         a.off_g = (unsigned long long)((char *)y.g - net->arena); a.off_w = (unsigned long long)((char *)y.w - net->arena);
-        a.off_v = (unsigned long long)((char *)y.v - net->arena); a.off_wn = (unsigned long long)((char *)y.wn - net->arena);
+        a.off_v = (unsigned long long)((char *)y.v - net->arena);
+        a.off_wn = y.wn ? (unsigned long long)((char *)y.wn - net->arena) : 0ull;
+        a.f32_operand = y.wn == nullptr;   // TF32 nets: the FP32 master array is the operand every rank reads
+        a.timeout_ns = net->dp_timeout_ns;
         a.n4 = (long long)y.in * y.ld_n / 4;
         a.scale = scale; a.momentum = momentum;
         a.seq = ++net->dp_seq;
         long long blocks = (a.n4 / net->world + dp::DP_THREADS - 1) / dp::DP_THREADS;
         if (blocks > net->dp_ctas) blocks = net->dp_ctas;
         if (blocks < 1) blocks = 1;
+        ProfPair pp;
+        B2_TRY(prof_begin(net, 1, us, &pp));
         dp::reduce_update_kernel<<<(int)blocks, dp::DP_THREADS, 0, us>>>(a);
+        B2_TRY(prof_end(us, pp));
         net->launches++;
         B2_CHECK_CUDA(cudaGetLastError());
     } else {
@@ -601,6 +634,32 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
     if (us != net->stream) {
         B2_CHECK_CUDA(cudaEventRecord(net->upd_done[l], us));
         net->upd_pending[l] = 1;
+    }
+    return B2NN_OK;
+}
+
+// A bounded cross-GPU wait of the exchange kernel (dp_kernels.cuh) or of K1's grid barrier gave up: the word it left
+// behind becomes B2NN_ERR_CUDA here.  Called where the host synchronises anyway (b2nn_sync, calls that return data).
+int check_device_error_words(b2nn_net *net) {
+    if (net->world > 1 && !net->peer_arena.empty() && net->arena) {
+        unsigned int e = 0;
+        B2_CHECK_CUDA(cudaMemcpyAsync(&e, net->arena + offsetof(dp::Flags, error), sizeof e, cudaMemcpyDeviceToHost,
+                                      net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        if (e != 0) {
+            const unsigned int kind = e >> 24, layer = (e >> 8) & 0xffffu, peer = e & 0xffu;
+            set_error("data-parallel exchange timed out on rank %d: %s (layer %u, peer rank %u) -- a peer process died or "
+                      "stalled; the weights of this net are no longer consistent",
+                      net->rank, kind == 1 ? "a peer's gradient never became ready" : kind == 2 ? "a peer never finished "
+                      "writing its slice" : "the launch's first CTA never released the others", layer, peer);
+            return B2NN_ERR_CUDA;
+        }
+    }
+    if (net->fused.bar) {
+        unsigned long long e = 0;
+        B2_CHECK_CUDA(cudaMemcpyAsync(&e, net->fused.bar + 1, sizeof e, cudaMemcpyDeviceToHost, net->stream));
+        B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+        B2_REQUIRE(e == 0, B2NN_ERR_CUDA, "the fused FP64 training kernel gave up waiting at a grid barrier (%llu polls)", e);
     }
     return B2NN_OK;
 }
@@ -649,6 +708,16 @@ int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *
     wide::eval_rows<<<(rows + 7) / 8, 256, 0, net->stream>>>(b.logits, pad8(dL), labels_dev, rows, dL, net->kind,
                                                              net->last_act, (float)net->last_param, pred_dev,
                                                              want_loss ? b.row_loss : nullptr);
+    net->launches++;
+    B2_CHECK_CUDA(cudaGetLastError());
+    return B2NN_OK;
+}
+
+// propagate's output pass (src/NeuralNet.java:16): logits of the last forward -> P_dev[rows][dL] doubles
+int wide_propagate_rows(b2nn_net *net, int rows, double *P_dev) {
+    const int L = net->n_dims - 1, dL = net->dims[L];
+    wide::propagate_rows<<<(rows + 7) / 8, 256, 0, net->stream>>>(net->wb.logits, pad8(dL), rows, dL, net->kind,
+                                                                  net->last_act, net->last_param, P_dev);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;

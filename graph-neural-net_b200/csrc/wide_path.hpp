@@ -20,8 +20,10 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
 int wide_forward(b2nn_net *net, int B);
 int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev = nullptr);
 int wide_join(b2nn_net *net);
+int check_device_error_words(b2nn_net *net);
 int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum);
 int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss);
+int wide_propagate_rows(b2nn_net *net, int rows, double *P_dev);
 int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,
                 long long *hits_dev);
 int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B, cudaStream_t st);

@@ -3,8 +3,10 @@
 global mini-batch, run forward/backward locally, and one all-reduce(sum) per weight matrix gives the
 single-device gradient; the update divides by the GLOBAL batch size (S:333, `batch.size()`).
 
-One process per GPU (torchrun); `torch.distributed` is plumbing only (rendezvous + shipping the
-NCCL unique id); the gradient all-reduce itself is issued by libb2nn.so on its own stream.
+One process per GPU (torchrun); `torch.distributed` is plumbing only (rendezvous + shipping the NCCL unique id, the
+CUDA IPC handles or the (pid, fd) pairs of the multicast set-up); the exchange itself -- by default ONE fused
+reduce-scatter + momentum update + all-gather kernel per layer over NVLink peer memory, summing inside the NVSwitch from
+4 GPUs up; NCCL all-reduce + update as the baseline -- is issued by libb2nn.so on its own stream.
 """
 import os
 
@@ -47,11 +49,7 @@ def init_comm(net, dist, rank=None, world=None):
     # 0.769 ms against 0.848 ms for plain peer memory), plain peer memory at 2 (there multimem sends the local
     # half through the switch as well: 0.799 against 0.768 ms).  profiles/r01_scaling.md has the runs.
     mode = os.environ.get("B2NN_DP") or ("nvls" if world >= 4 else "p2p")
-    from . import _capi as capi
-    if getattr(net, "precision", None) == capi.PREC_TF32:
-        # TF32 nets have no BF16 operand copy for the fused kernel to replicate: per-layer NCCL all-reduce of the
-        # FP32 gradient + the local update, every replica keeping its full FP32 master (= operand) array
-        mode = "nccl"
+    # (TF32 nets take the same exchanges: the fused kernel replicates their FP32 weights instead of a BF16 copy)
     if world > 1 and mode == "nvls":
         if _init_nvls(net, dist, rank, world):
             return rank, world
@@ -83,10 +81,13 @@ def _init_nvls(net, dist, rank, world):
     mine = net.commNvlsExport()
     pairs = [None] * world
     dist.all_gather_object(pairs, mine)
-    if any(p is None for p in pairs):
-        if mine is not None:
-            raise RuntimeError("multicast support differs between ranks")
+    if all(p is None for p in pairs):
         return False
+    if any(p is None for p in pairs):
+        # every rank sees the same gathered list, so every rank raises (a rank raising alone would leave the others
+        # waiting in the next collective); the ranks that did export have moved their arena: re-create the net
+        raise RuntimeError("NVSwitch multicast support differs between ranks: rank(s) %s lack it (set B2NN_DP=p2p)"
+                           % [r for r, p in enumerate(pairs) if p is None])
 
     def stage(what, fn):
         try:

@@ -198,6 +198,23 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_profile_read(self._h, C.byref(ms), C.byref(n), C.byref(fl)))
         return ms.value, n.value, fl.value
 
+    K1_PHASES = ("stage", "phase1", "barrier1", "phase2", "barrier2", "p3:delta2", "phase4", "p5:W2", "p3:a2", "p3:z3",
+                 "p3:softmax", "p3:loss", "p5:W0", "p5:W1c", "p5:W1r", "stage:wait")
+
+    def k1Profile(self, on=True):
+        """switch K1's per-phase cycle counters on / off; returns ({phase: cycles per step}, steps) of the last
+        profiled launch"""
+        cyc = (C.c_double * 16)()
+        n = C.c_int32(0)
+        capi.check(capi.lib().b2nn_k1_profile(self._h, int(on), cyc, C.byref(n)))
+        return dict(zip(self.K1_PHASES, [float(c) for c in cyc])), n.value
+
+    def profileReadClasses(self):
+        """{class: (ms, launches)} of the profiled pass: contraction, update, output, prologue"""
+        ms, n = (C.c_double * 4)(), (C.c_int64 * 4)()
+        capi.check(capi.lib().b2nn_profile_read_classes(self._h, ms, n))
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(("contraction", "update", "output", "prologue"))}
+
     def commInit(self, unique_id, rank, world):
         buf = C.create_string_buffer(bytes(unique_id), 128)
         capi.check(capi.lib().b2nn_comm_init(self._h, buf, rank, world))

@@ -229,6 +229,15 @@ int b2nn_kernel_launches(const b2nn_net *net, int64_t *n);
  * launch count and algorithmic FLOPs (2*M*N*K per launch) since profiling was switched on. */
 int b2nn_profile_enable(b2nn_net *net, int32_t on);
 int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, double *gemm_flops);
+/* the same pass itemised by kernel class: [0] contractions, [1] momentum update / cross-GPU exchange, [2] output delta
+ * (softmax-CE gradient), [3] input prologue: summed device time (ms) and launch count of each since profiling was
+ * switched on (the side-stream work is serialised while profiling, so every kernel is timed alone) */
+int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4);
+/* Measurement aid for K1 (the persistent fused FP64 training kernel): while `on`, every K1 launch collects the cycle
+ * counters of CTA 0 per phase (and synchronises); cycles16_or_null receives the per-step averages of the LAST such
+ * launch in the order stage, phase1, barrier1, phase2, barrier2, p3:delta2, phase4, p5:W2, p3:a2, p3:z3, p3:softmax,
+ * p3:loss, p5:W0, p5:W1c, p5:W1r, stage:wait; steps_or_null its step count.  The call first returns, then sets `on`. */
+int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t *steps_or_null);
 int b2nn_device_count(int32_t *n);
 int b2nn_version(void);
 const char *b2nn_last_error(void);

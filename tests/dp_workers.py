@@ -105,13 +105,21 @@ def gloo_init_comm_worker(rank, world, port, out_dir):
             net = _RecordingNet(rank, multicast)
             g.dp.init_comm(net, dist)
             out[(mode, multicast)] = net.calls
-        # a TF32 net gets the NCCL exchange whatever B2NN_DP asks for (no BF16 operand copy to replicate)
+        # a TF32 net takes the same exchange set-ups as a BF16 net
         for mode in ("p2p", "nvls"):
             os.environ["B2NN_DP"] = mode
             net = _RecordingNet(rank, True)
             net.precision = g.capi.PREC_TF32
             g.dp.init_comm(net, dist)
             out[("tf32", mode)] = net.calls
+        # multicast support on rank 0 only: every rank must raise
+        os.environ["B2NN_DP"] = "nvls"
+        net = _RecordingNet(rank, rank == 0)
+        try:
+            g.dp.init_comm(net, dist)
+            out["mixed"] = "no exception"
+        except RuntimeError as e:
+            out["mixed"] = str(e)
         # a stage failing on ONE rank must raise on EVERY rank (nobody is left waiting in a collective)
         os.environ["B2NN_DP"] = "nvls"
         net = _RecordingNet(rank, True)

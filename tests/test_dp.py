@@ -61,33 +61,57 @@ def test_gloo_world2_init_comm_sequences(g, tmp_path):
         assert c[("nvls", True)][1:] == [("nvls_export",), ("nvls_import", pairs), ("nvls_team", team_arg),
                                          ("nvls_bind",)]
         assert c[("nvls", False)][1:] == [("nvls_export",), ("ipc_export",), ("ipc_import", [0, 1])]
-        assert c[("tf32", "p2p")] == c[("tf32", "nvls")] == [("init", b"u" * 128, r, 2)]   # TF32 nets: NCCL exchange only
+        # TF32 nets take the same exchanges as BF16 nets (the fused kernel replicates their FP32 weights)
+        assert c[("tf32", "p2p")] == c[("p2p", True)] and c[("tf32", "nvls")] == c[("nvls", True)]
+        # multicast support on one rank only: EVERY rank raises (nobody is left waiting in a collective)
+        assert "rank(s) [1] lack it" in c["mixed"]
         assert "rank(s) [1]" in c["failure"] and "999" in c["failure"]     # raised on both ranks, naming rank 1
 
 
+def _multicast_supported():
+    """CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED of device 0 (None when it cannot be queried)"""
+    try:
+        from cuda.bindings import driver as cu
+    except Exception:
+        try:
+            from cuda import cuda as cu
+        except Exception:
+            return None
+    try:
+        cu.cuInit(0)
+        err, dev = cu.cuDeviceGet(0)
+        err, val = cu.cuDeviceGetAttribute(cu.CUdevice_attribute.CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev)
+        return bool(val) if int(err) == 0 else None
+    except Exception:
+        return None
+
+
 @pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("mode", ["p2p", "nccl", "nvls"])
-def test_world2_matches_single_gpu(g, tmp_path, mode, monkeypatch):
-    """2 GPUs x 256 rows vs 1 GPU x 512 rows, with (nvls) the fused kernel summing inside the NVSwitch
-    (multimem.ld_reduce) and replicating the weights with multimem.st -- falls back to p2p where the box has
-    no multicast support --, (p2p) the fused reduce-scatter/update/all-gather kernel over
-    NVLink peer memory and sharded optimizer state, and (nccl) the per-layer NCCL all-reduce + update: replicas
-    bit-identical, weights equal to the single-GPU run within FP32 re-association of the batch sum (tolerance:
-    2e-3 of the update's Frobenius norm per run of 6 steps; BF16 operands are identical, only the FP32 sum
-    order differs)."""
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_world_matches_single_gpu(g, tmp_path, mode, world, prec, monkeypatch):
+    """G GPUs x 256 rows vs 1 GPU x G*256 rows (G = 2, 4, 8 by device count), with (nvls) the fused kernel summing
+    inside the NVSwitch (multimem.ld_reduce) and replicating the weights with multimem.st, (p2p) the fused
+    reduce-scatter/update/all-gather kernel over NVLink peer memory and sharded optimizer state, and (nccl) the
+    per-layer NCCL all-reduce + update: replicas bit-identical, weights equal to the single-GPU run within FP32
+    re-association of the batch sum (tolerance: 2e-3 of the update's Frobenius norm per run of 6 steps; the operands
+    are identical, only the FP32 sum order differs).  Where the device reports multicast support the nvls run must
+    really have used it (a silent fall-back to p2p fails the test); without support it is skipped."""
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    if mode == "nvls" and _multicast_supported() is False:
+        pytest.skip("no NVSwitch multicast support on this box")
     import torch.multiprocessing as mp
     from tests import dp_workers
     monkeypatch.setenv("B2NN_DP", mode)
-    mp.spawn(dp_workers.nccl_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(dp_workers.nccl_worker, args=(world, _free_port(), str(tmp_path), prec), nprocs=world, join=True)
     r = np.load(tmp_path / "nccl.npz")
     assert int(r["replicas_equal"]) == 1
     du_dp, du_1 = r["w_dp"] - r["w0"], r["w_single"] - r["w0"]
     rel = np.linalg.norm(du_dp - du_1) / np.linalg.norm(du_1)
     assert rel < 2e-3, rel
     assert int(r["launches"]) > 0
-    assert str(r["mode"]) in ((mode, "p2p") if mode == "nvls" else (mode,))
-    print("exchange:", str(r["mode"]))
-
+    assert str(r["mode"]) == mode, (str(r["mode"]), mode)
+    print("exchange:", str(r["mode"]), "rel", rel)

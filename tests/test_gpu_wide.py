@@ -242,6 +242,61 @@ def test_eval_argmax_last_max_wins(g):
     assert hits == 40 and (pred == 15).all()                # MNISTTrainer.java:166-168
 
 
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_eval_argmax_compares_activated_outputs(g, prec):
+    """M:164-168 compares the ACTIVATED outputs with `>=` from index 0: with a ReLU output layer every row whose
+    logits are all negative ties at 0 and the LAST index wins (argmax of the logits would pick another class); rows
+    with a positive logit keep its index; equal positive outputs -> the later index."""
+    dL, d0 = 16, 64
+    net = g.GeneralNeuralNet([d0, dL], g.IDENTITY, g.IDENTITY_PRIME, g.RELU, g.RELU_PRIME, g.HALF_SQUARED_ERROR,
+                             g.HALF_SQUARED_ERROR_PRIME,
+                             precision=g.capi.PREC_BF16 if prec == "bf16" else g.capi.PREC_TF32)
+    W = np.zeros((d0, dL))
+    W[0, :] = -np.arange(1, dL + 1) / 8.0        # logits of rows with x[0] = 1: all negative, largest at index 0
+    W[1, 3] = 2.0                                # rows with x[1] = 1 as well: index 3 positive
+    W[2, 5] = W[2, 9] = 1.0                      # rows with x[2] = 1: indices 5 and 9 tie at a positive value
+    net.setWeights(W.ravel())
+    x = np.zeros((48, d0), dtype=np.float32)
+    x[:, 0] = 1.0
+    x[16:32, 1] = 1.0
+    x[32:, 0] = 0.0
+    x[32:, 2] = 4.0
+    lab = np.concatenate([np.full(16, dL - 1), np.full(16, 3), np.full(16, 9)]).astype(np.int32)
+    ds = g.Dataset(net, x, labels=lab)
+    hits, _, pred = ds.evaluate(want_pred=True)
+    assert (pred == lab).all() and hits == 48, pred
+    y = net.propagate(x.astype(np.float64))
+    ref = np.array([max(i for i in range(dL) if r[i] >= r.max()) for r in y])
+    assert (pred == ref).all()
+
+
+@pytest.mark.parametrize("kind", ["softmax", "general"])
+def test_propagate_output_pass_on_device(g, kind):
+    """NeuralNet.propagate (src/NeuralNet.java:16) of a tensor-core net: softmax (S:357-376) / last activation
+    (G:214-218) of the FP32 logits is computed on the device in double -- equal to numpy on the same logits"""
+    d0, dL, n = 96, 40, 50
+    rng = np.random.RandomState(12)
+    W = bf16_round(rng.randn(d0, dL) * 0.3)
+    x = bf16_round(rng.rand(n, d0))
+    if kind == "softmax":
+        net = g.SoftmaxCrossEntropyNeuralNet([d0, dL], g.IDENTITY, g.IDENTITY_PRIME, precision=g.capi.PREC_BF16,
+                                             flags=g.capi.FLAG_STABLE_SOFTMAX)
+    else:
+        net = g.GeneralNeuralNet([d0, dL], g.IDENTITY, g.IDENTITY_PRIME, g.TANH, g.TANH_PRIME, g.HALF_SQUARED_ERROR,
+                                 g.HALF_SQUARED_ERROR_PRIME, precision=g.capi.PREC_BF16)
+    net.setWeights(W.ravel())
+    z = (x @ W).astype(np.float32).astype(np.float64)
+    if kind == "softmax":
+        e = np.exp(z - z.max(axis=1, keepdims=True))
+        ref = e / e.sum(axis=1, keepdims=True)
+    else:
+        ref = np.tanh(z)
+    y = net.propagate(x)
+    assert np.abs(y - ref).max() <= 5e-6    # FP32 accumulation order of the logits; the output pass itself is double
+    if kind == "softmax":
+        assert np.abs(y.sum(axis=1) - 1.0).max() <= 1e-12
+
+
 @pytest.mark.parametrize("d0", [256, 100])   # 100: rows not 8-byte aligned, scalar load path
 def test_pixel_byte_rows_match_float_rows(g, d0):
     """rows kept as IDX pixel bytes in pinned host memory (B2NN_DT_U8, value = (raw & 0xff) / 255.0 as in M:97) against

@@ -1,30 +1,167 @@
-"""Full-size (BASELINE configs[3]: 4096-4096-4096-1000, batch 4096) checks of the tensor-core path through
-size-independent properties -- the FP64 oracle needs minutes per sample at this width (bench.py cpu_baseline), so
-parity at full size rests on what the reference's definition of the batch gradient implies:
-  * gradientStep sums per-sample gradients over the batch (S:305-322) and divides by batch.size() (S:333), so with
-    momentum 0 the update of the full batch is the mean of the updates of its two halves;  per-row quantities do
-    not depend on which other rows share the batch, so only the FP32 summation order of the gradient contraction
-    (K = 4096 in one accumulator against two K = 2048 accumulators averaged in FP64) differs:  <= 1e-3 relative
-    (Frobenius, per layer; the same bound family as the 2e-3 of the cross-GPU sum in tests/test_dp.py -- 256 against
-    128 FP32 accumulator updates of possibly truncating tensor-core adds stay below ~2e-5);
-  * the same step on two nets built alike is bit-identical (fixed tile order, fixed reduction order).
-The data-parallel tests (tests/test_dp.py) check the same sum across GPUs at small sizes."""
+"""Full-size checks of the tensor-core path (BASELINE configs[3]: 4096-4096-4096-1000, batch 4096; configs[4]:
+8192-wide layers) through the C-ABI.  The FP64 oracle needs minutes per sample at this width (bench.py
+cpu_baseline), so at full size the comparison partner is
+
+  * for a BARE contraction: the exact product of the operands rounded the way the tensor core reads them
+    (BF16 / TF32), accumulated in FP64 by numpy -- the three operand major-ness combinations of a training step
+    (forward K-major x MN-major, delta K-major x K-major, gradient MN-major x MN-major with K = batch), each isolated
+    by choosing weights / inputs that make the other contractions of the step exact (zeros, identity matrix);
+  * for a whole gradientStep (S:297-346): the numpy rounding models of tests/test_gpu_wide.py / test_gpu_z_tf32.py
+    (validated against the oracle at widths the oracle can run) evaluated at full size;
+  * size-independent properties: with momentum 0 the update of the full batch is the mean of the updates of its two
+    halves (the batch sum S:305-322 divided by batch.size() S:333), and a step is deterministic.
+4096^3 on 74 CTA pairs is 3.46 waves, so these shapes are also the only ones that reach the half-tile tail wave with
+every pair busy."""
 import numpy as np
 import pytest
+
+from tests.test_gpu_wide import bf16_round, emulate_bf16_step
+from tests.test_gpu_z_tf32 import emulate_tf32_step, tf32_round
 
 pytestmark = pytest.mark.gpu
 
 DIMS, B = [4096, 4096, 4096, 1000], 4096
+ROUND = {"bf16": bf16_round, "tf32": tf32_round}
+# bare contraction against exact-operand FP64: what is left is the FP32 accumulation order
+BARE_TOL = {"bf16": 1e-3, "tf32": 5e-5}
 
 
-def make(g, precision):
-    return g.SoftmaxCrossEntropyNeuralNet(DIMS, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=precision,
+def prec_id(g, prec):
+    return g.capi.PREC_BF16 if prec == "bf16" else g.capi.PREC_TF32
+
+
+def make(g, precision, dims=DIMS):
+    return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=precision,
                                           flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX)
+
+
+def identity_net(g, dims, precision):
+    """GeneralNeuralNet with identity activations everywhere and half squared error: every epilogue is a plain store"""
+    return g.GeneralNeuralNet(dims, g.IDENTITY, g.IDENTITY_PRIME, g.IDENTITY, g.IDENTITY_PRIME,
+                              g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, precision=precision)
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+@pytest.mark.parametrize("M,K,N", [(4096, 4096, 4096), (2048, 8192, 8192)])
+def test_bare_forward_contraction_full_size(g, prec, M, K, N):
+    """y = x W (S:187-192): A K-major, B MN-major, FP32 store epilogue"""
+    rnd = ROUND[prec]
+    net = identity_net(g, [K, N], prec_id(g, prec))
+    rng = np.random.RandomState(K + N)
+    W = rnd(rng.randn(K, N) * 0.05)
+    x = rnd(rng.randn(M, K))
+    net.setWeights(W.ravel())
+    y = net.propagate(x)
+    ref = x @ W
+    err = np.abs(y - ref).max()
+    assert err <= BARE_TOL[prec] * np.abs(ref).max(), (prec, err, np.abs(ref).max())
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+@pytest.mark.parametrize("Bt,K,N", [(4096, 4096, 4096), (1024, 8192, 8192)])
+def test_bare_gradient_contraction_full_size(g, prec, Bt, K, N):
+    """G = A^T D (S:279-283 + S:305-317): both operands MN-major, K = batch.  With W = 0 the output is 0, so the
+    output delta is exactly -t (S: loss' = a - t, identity f' = 1), and with step 1 and a power-of-two batch the stored
+    velocity is G / B without rounding."""
+    rnd = ROUND[prec]
+    net = identity_net(g, [K, N], prec_id(g, prec))
+    net.setWeights(np.zeros(net.numWeights))
+    rng = np.random.RandomState(Bt + N)
+    x = rnd(rng.randn(Bt, K))
+    t = rnd(rng.randn(Bt, N))
+    net.gradientStep((x, t), 1.0, 0.0)
+    v = net.getVelocity().reshape(K, N) * Bt
+    ref = -(x.T @ t)
+    err = np.abs(v - ref).max()
+    assert err <= BARE_TOL[prec] * np.abs(ref).max(), (prec, err, np.abs(ref).max())
+    assert np.array_equal(net.getWeights().reshape(K, N) * Bt, -v)          # W -= v from zero (S:338)
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_bare_delta_contraction_full_size(g, prec):
+    """D_1 = D_2 W_1^T (S:272-278): both operands K-major.  W_0 = 0 makes a_1 = 0, the output 0 and D_2 = -t; the batch
+    is the 4096 x 4096 identity matrix, so the layer-0 gradient A_0^T D_1 is D_1 itself (one non-zero product per sum)
+    and the stored velocity of W_0 is D_1 / B."""
+    n = 4096
+    rnd = ROUND[prec]
+    net = identity_net(g, [n, n, n], prec_id(g, prec))
+    rng = np.random.RandomState(77)
+    W1 = rnd(rng.randn(n, n) * 0.05)
+    t = rnd(rng.randn(n, n))
+    net.setWeights(np.concatenate([np.zeros(n * n), W1.ravel()]))
+    net.gradientStep((np.eye(n), t), 1.0, 0.0)
+    v = net.getVelocity()
+    d1 = v[:n * n].reshape(n, n) * n
+    ref = -(t @ W1.T)
+    # BF16 nets store D_1 rounded to BF16 (relative 2^-9), TF32 nets keep FP32
+    slack = 2.0 ** -8 * np.abs(ref) if prec == "bf16" else 0.0
+    assert np.all(np.abs(d1 - ref) <= BARE_TOL[prec] * np.abs(ref).max() + slack), np.abs(d1 - ref).max()
+    assert not v[n * n:].any()                                              # a_1 = 0: no gradient for W_1
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_c4_full_step_vs_rounding_model(g, prec):
+    """one gradientStep of the real C4 against the numpy model that rounds where the kernels round, evaluated at full
+    size: per-layer update within 1e-2 (BF16) / 1e-3 (TF32) Frobenius, batch loss within 1e-3 / 1e-4"""
+    tol, ltol, emu = {"bf16": (1e-2, 1e-3, emulate_bf16_step), "tf32": (1e-3, 1e-4, emulate_tf32_step)}[prec]
+    rng = np.random.RandomState(8)
+    x = rng.rand(B, DIMS[0]).astype(np.float32)
+    lab = rng.randint(0, DIMS[-1], B).astype(np.int32)
+    net = make(g, prec_id(g, prec))
+    w0 = net.getWeights()
+    loss = net.gradientStepLabeled(x, lab, 0.01, 0.0, returnLoss=True)
+    v = net.getVelocity()
+    net.close()
+    emu_loss, emu_v = emu(DIMS, w0, x, lab, 0.01)
+    assert abs(loss - emu_loss) <= ltol * max(1.0, abs(emu_loss)), (loss, emu_loss)
+    off = 0
+    for l in range(len(DIMS) - 1):
+        n = DIMS[l] * DIMS[l + 1]
+        a, e = v[off:off + n], emu_v[l].ravel()
+        rel = np.linalg.norm(a - e) / np.linalg.norm(e)
+        assert rel <= tol, (prec, l, rel)
+        off += n
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_six_matrix_net_vs_oracle(g, orc, prec):
+    """BASELINE configs[4]'s shape (7 dims = 6 weight matrices, 1000 classes) at a width the oracle can run: first step
+    against the rounding model (tight) and the FP64 oracle (loose: leaky-ReLU slope flips compound through five hidden
+    layers), then two more momentum steps with the batch loss tracked against the oracle's"""
+    dims, Bs = [384] * 6 + [1000], 128
+    tol, otol, cos_min, emu = {"bf16": (1e-2, 2e-1, 0.98, emulate_bf16_step),
+                               "tf32": (1e-3, 5e-2, 0.998, emulate_tf32_step)}[prec]
+    net = make(g, prec_id(g, prec), dims)
+    ref = orc.OracleNet(dims)
+    ref.set_weights(net.getWeights())
+    rng = np.random.RandomState(21)
+    x = rng.rand(Bs, dims[0])
+    lab = rng.randint(0, dims[-1], Bs).astype(np.int32)
+    t = np.zeros((Bs, dims[-1]))
+    t[np.arange(Bs), lab] = 1.0
+    w0 = ref.get_weights()
+    emu_loss, emu_v = emu(dims, w0, x, lab, 0.05)
+    for it in range(3):
+        ref_loss = np.mean([ref.loss(x[i], t[i]) for i in range(Bs)])
+        loss = net.gradientStepLabeled(x.astype(np.float32), lab, 0.05, 0.9, returnLoss=True)
+        ref.gradient_step(x, t, 0.05, 0.9)
+        assert abs(loss - ref_loss) <= 2e-2 * max(1.0, abs(ref_loss)), (it, loss, ref_loss)
+        if it == 0:
+            assert abs(loss - emu_loss) <= 1e-3 * max(1.0, abs(emu_loss))
+            du, du_ref = w0 - net.getWeights(), w0 - ref.get_weights()
+            off = 0
+            for l in range(len(dims) - 1):
+                n = dims[l] * dims[l + 1]
+                a, r, e = du[off:off + n], du_ref[off:off + n], emu_v[l].ravel()
+                assert np.linalg.norm(a - e) <= tol * np.linalg.norm(e), (l, np.linalg.norm(a - e) / np.linalg.norm(e))
+                assert np.linalg.norm(a - r) <= otol * np.linalg.norm(r), (l, np.linalg.norm(a - r) / np.linalg.norm(r))
+                assert a @ r >= cos_min * np.linalg.norm(a) * np.linalg.norm(r)
+                off += n
 
 
 @pytest.mark.parametrize("prec", ["bf16", "tf32"])
 def test_c4_full_batch_update_is_the_mean_of_its_halves(g, prec):
-    precision = g.capi.PREC_BF16 if prec == "bf16" else g.capi.PREC_TF32
+    precision = prec_id(g, prec)
     rng = np.random.RandomState(4)
     x = rng.rand(B, DIMS[0]).astype(np.float32)
     lab = rng.randint(0, DIMS[-1], B).astype(np.int32)
