@@ -1,19 +1,24 @@
 #!/usr/bin/env python
 """bench.py -- headline measurement of the b2nn hot path (train samples/s).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b2nn|reference] [--workload c4|c5|c2]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b2nn|reference] [--workload c4|c5|c2|c1|c3]
 
-One "step" = one mini-batch gradient step (forward, backprop, momentum-SGD update).  Default
-workload is BASELINE.json's 4096-wide MLP (configs[3]: synthetic 4096-4096-4096-1000, batch 4096
-per GPU, BF16 tcgen05 GEMMs); with N > 1 ranks the global batch is N x 4096 (weak scaling), each
-rank runs forward/backward on its 4096 rows and the per-layer gradients are all-reduced with NCCL.
-Prints ONE JSON line on rank 0 (contract: see the task statement / DESIGN.md "Measurement").
+One "step" = one mini-batch gradient step (forward, backprop, momentum-SGD update; the reference's
+gradientStep, src/SoftmaxCrossEntropyNeuralNet.java:297-346).  Default workload is BASELINE.json's 4096-wide MLP
+(configs[3]: synthetic 4096-4096-4096-1000, batch 4096 per GPU, BF16 tcgen05 GEMMs); with N > 1 ranks the global batch
+is N x 4096 (weak scaling), each rank runs forward/backward on its 4096 rows and every layer's gradient is exchanged by
+ONE fused reduce-scatter + momentum update + all-gather kernel over NVLink (in-switch reduction from 4 GPUs up;
+B2NN_DP=nccl selects the NCCL all-reduce + update baseline).  BASELINE configs[4] (8192-wide, 6 matrices, GLOBAL batch
+32768 = strong scaling) is measured beside it at every N (`also.c5`), the tiny FP64 configs and the TF32 mode at N = 1.
+Prints ONE JSON line on rank 0 (contract: see DESIGN.md "Measurement").
 
---impl reference times the reference's CPU algorithm for the same workload: the Java trainer
-cannot run here (no JVM on this box), so it is the oracle's faithful C restatement, 1 thread like
-the serial reference, on a bounded sample of the same workload.
+--impl reference times the reference's CPU algorithm for the same workload: the Java trainer cannot run here (no JVM
+on this box), so it is the oracle's faithful C restatement, 1 thread like the serial reference, on a bounded sample of
+the same workload.
 """
 import argparse
+import ctypes as C
+import hashlib
 import json
 import os
 import sys
@@ -26,23 +31,23 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: dims, per-GPU batch, precision, step size
-    "c4": dict(dims=[4096, 4096, 4096, 1000], batch=4096, prec="bf16", step=0.01,
+    # name: dims, batch (per GPU for weak scaling, GLOBAL for strong scaling), precision, step size
+    "c4": dict(dims=[4096, 4096, 4096, 1000], batch=4096, prec="bf16", step=0.01, scaling="weak",
                desc="synthetic 4096-4096-4096-1000 MLP, batch 4096 per GPU, BF16 tcgen05 GEMMs (BASELINE configs[3])"),
-    "c5": dict(dims=[8192] * 6 + [1000], batch=4096, prec="bf16", step=0.01,
-               desc="synthetic 8192-wide 6-matrix MLP (8192x6 -> 1000), batch 4096 per GPU = global 32768 at 8 GPUs "
+    "c5": dict(dims=[8192] * 6 + [1000], batch=32768, prec="bf16", step=0.01, scaling="strong",
+               desc="synthetic 8192-wide 6-matrix MLP (8192x6 -> 1000), GLOBAL batch 32768 split over the GPUs "
                     "(BASELINE configs[4])"),
-    "c2": dict(dims=[784, 300, 100, 10], batch=16, prec="f64", step=0.0125,
+    "c2": dict(dims=[784, 300, 100, 10], batch=16, prec="f64", step=0.0125, scaling="replicas",
                desc="784-300-100-10 Softmax/CE, batch 16, FP64 parity mode (BASELINE configs[1])"),
-    "c1": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01,
+    "c1": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01, scaling="replicas",
                desc="784-100-50-10 SoftmaxCrossEntropyNeuralNet, batch 8, FP64 parity mode (BASELINE configs[0], "
                     "logs/trainLog.csv:3)"),
-    "c3": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01, general=True,
+    "c3": dict(dims=[784, 100, 50, 10], batch=8, prec="f64", step=0.01, general=True, scaling="replicas",
                desc="GeneralNeuralNet 784-100-50-10, sigmoid inner / outer, half squared error, batch 8, FP64 parity "
                     "mode (BASELINE configs[2])"),
 }
 CPU_SAMPLE_ROWS = {"c4": 4, "c5": 2, "c2": 16, "c1": 8, "c3": 8}
-
+CPU_SAMPLE_STEPS = {"c4": (10, 1), "c5": (3, 1), "c2": (500, 20), "c1": (3000, 50), "c3": (1500, 50)}  # ~10-15 s each
 
 _REAL_STDOUT = None
 
@@ -62,14 +67,30 @@ def flops_per_sample(dims):
     return 6 * n_weights(dims) - 2 * dims[0] * dims[1]
 
 
-def measured_peaks():
+def measured_peaks(tf32=False):
+    """roofline denominators: MEASURED_PEAKS.json (driver-written cuBLAS BF16 rates: burst = a kernel timed alone,
+    sustained = seconds-long loop under the power cap); profiles/tf32_peaks.json holds the same two numbers for
+    torch.matmul FP32 with allow_tf32, measured by scratch/tf32_peak.py on this pool's B200"""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         with open(p) as f:
             d = json.load(f)
-        return dict(tflops=float(d.get("bf16_tflops_sustained", d.get("bf16_tflops"))), hbm=float(d["hbm_gbs"]),
-                    src="measured (MEASURED_PEAKS.json, bf16 sustained)")
-    return dict(tflops=1590.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+        pk = dict(burst=float(d["bf16_tflops"]), sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                  hbm=float(d["hbm_gbs"]), src="measured (MEASURED_PEAKS.json: cuBLAS bf16 8192^3)")
+    else:
+        pk = dict(burst=1590.0, sustained=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+    if tf32:
+        tp = os.path.join(ROOT, "profiles", "tf32_peaks.json")
+        if os.path.exists(tp):
+            with open(tp) as f:
+                d = json.load(f)
+            pk = dict(pk, burst=float(d["tf32_tflops"]), sustained=float(d["tf32_tflops_sustained"]),
+                      src="measured (profiles/tf32_peaks.json: torch.matmul fp32 allow_tf32 8192^3, same method as "
+                          "MEASURED_PEAKS.json)")
+        else:
+            pk = dict(pk, burst=1100.0, sustained=1100.0, src="nominal dense TF32 peak (B200_PROFILING.md): no measured "
+                                                              "TF32 peak on file")
+    return pk
 
 
 class ClockSampler:
@@ -80,8 +101,9 @@ class ClockSampler:
                0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, index):
-        self.index, self.proc, self.active, self.t0 = index, None, False, None
-        self.windows = []
+        self.index, self.proc, self.t0 = index, None, None
+        self.windows = []   # (t0, t1, tag)
+        self.rows = None
 
     def start(self):
         import subprocess
@@ -96,15 +118,18 @@ class ClockSampler:
     def begin(self):
         self.t0 = time.time()
 
-    def end(self):
+    def end(self, tag="main"):
         if self.t0 is not None:
-            self.windows.append((self.t0, time.time()))
+            self.windows.append((self.t0, time.time(), tag))
             self.t0 = None
 
-    def summary(self):
+    def _collect(self):
         import datetime
+        if self.rows is not None:
+            return
+        self.rows = []
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["clock_sampling_unavailable"]}
+            return
         time.sleep(0.05)
         self.proc.terminate()
         try:
@@ -112,18 +137,25 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
             out = ""
-        clocks, reasons, mx, total = [], set(), None, 0
         for line in out.splitlines():
             f = [q.strip() for q in line.split(",")]
             if len(f) < 4:
                 continue
             try:
                 ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
-                mhz, mxv, mask = int(f[1]), int(f[2]), int(f[3], 16)
+                self.rows.append((ts, int(f[1]), int(f[2]), int(f[3], 16)))
             except Exception:
                 continue
-            total += 1
-            if not any(a - 0.02 <= ts <= b + 0.02 for a, b in self.windows):
+
+    def summary(self, tags=None):
+        """median SM clock and the reasons seen inside the windows whose tag is in `tags` (all windows when None);
+        ends the sampling process on first use"""
+        self._collect()
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["clock_sampling_unavailable"]}
+        clocks, reasons, mx = [], set(), None
+        for ts, mhz, mxv, mask in self.rows:
+            if not any(a - 0.02 <= ts <= b + 0.02 for a, b, t in self.windows if tags is None or t in tags):
                 continue
             clocks.append(mhz)
             mx = mxv
@@ -132,8 +164,8 @@ class ClockSampler:
                     reasons.add(name)
         clocks.sort()
         return {"sm_mhz": (clocks[len(clocks) // 2] if clocks else None), "sm_max_mhz": mx, "samples": len(clocks),
-                "samples_total": total, "reasons": sorted(reasons), "how": "nvidia-smi -lms 20 subprocess, samples "
-                "inside the timed regions (device-resident, roofline pass, e2e)"}
+                "samples_total": len(self.rows), "reasons": sorted(reasons),
+                "how": "nvidia-smi -lms 20 subprocess, samples inside the timed regions"}
 
 
 def synth_data(rows, d0, n_classes, seed, dtype):
@@ -178,6 +210,13 @@ def cpu_reference_run(workload, steps, warmup):
     return rows * steps / dt, dt, rows
 
 
+def cpu_baseline_block(workload):
+    cs, cw = CPU_SAMPLE_STEPS[workload]
+    val, dt, r = cpu_reference_run(workload, cs, cw)
+    return {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
+            "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" % (cs, r, dt)}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -189,7 +228,8 @@ def run_reference(args):
     out = {
         "impl": "reference", "metric": "train_samples_per_sec", "value": val, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if wl["scaling"] == "strong" else "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "dims": wl["dims"], "batch_per_step": rows},
         "cpu_baseline": {"value": val, "unit": "samples/s", "cores": 1, "kind": "port", "sample": sample,
                          "note": "the Java reference cannot run on this box (no JVM); oracle = C restatement, "
@@ -198,6 +238,325 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     emit(out)
+
+
+class Ctx:
+    """what every measurement needs: the package, torch, the process group, this rank, the clock sampler"""
+
+    def __init__(self, g, torch, dist, rank, world, local_rank, sampler):
+        self.g, self.torch, self.dist = g, torch, dist
+        self.rank, self.world, self.local_rank, self.sampler = rank, world, local_rank, sampler
+        self.stream = torch.cuda.current_stream()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def events(self):
+        return self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+
+
+def train_call(g, net, ds, idx, B, step, want_loss=False):
+    loss = np.empty(idx.shape[0]) if want_loss else None
+    g.capi.check(g.capi.lib().b2nn_train_indexed(
+        net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), idx.shape[0], B, step, 0.9,
+        loss.ctypes.data_as(C.POINTER(C.c_double)) if want_loss else None))
+    return loss
+
+
+def dp_check(ctx, net, make_single, dims, B, step):
+    """Data-parallel correctness inside the driver's own run: 3 steps with every rank on its B rows of a global batch of
+    world x B rows, against the same 3 steps of ONE net on rank 0 over the whole global batch (the reference's batch
+    sum S:305-322 divided by batch.size() S:333).  rel = |dW_dp - dW_1| / |dW_1| (only the FP32 order of the batch
+    sum differs; bound 2e-3 as in tests/test_dp.py); replicas_equal = every rank holds bit-identical weights."""
+    g, dist, rank, world = ctx.g, ctx.dist, ctx.rank, ctx.world
+    rng = np.random.default_rng(99)
+    n = world * B
+    x = rng.random((n, dims[0]), dtype=np.float32)
+    lab = rng.integers(0, dims[-1], n).astype(np.int32)
+    w0 = net.getWeights() if rank == 0 else None
+    mine = slice(rank * B, (rank + 1) * B)
+    for _ in range(3):
+        net.gradientStepLabeled(x[mine], lab[mine], step, 0.9)
+    net.sync()
+    ctx.barrier()
+    w_dp = net.getWeights()
+    digest = hashlib.sha1(w_dp.astype(np.float32).tobytes()).hexdigest()
+    digests = [None] * world
+    dist.all_gather_object(digests, digest)
+    res = [None]
+    if rank == 0:
+        single = make_single()
+        for _ in range(3):
+            single.gradientStepLabeled(x, lab, step, 0.9)
+        w1 = single.getWeights()
+        single.close()
+        du_dp, du_1 = w_dp - w0, w1 - w0
+        res[0] = {"rel": float(np.linalg.norm(du_dp - du_1) / np.linalg.norm(du_1)),
+                  "replicas_equal": all(d == digests[0] for d in digests), "exchange": net.commMode(), "steps": 3,
+                  "global_batch": n, "bound": 2e-3,
+                  "what": "3 data-parallel steps vs the same 3 steps of one net on rank 0 over the global batch"}
+    dist.broadcast_object_list(res, src=0)
+    ctx.barrier()
+    return res[0]
+
+
+def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, want_dp_check=True, e2e_rows="bf16"):
+    """one tensor-core workload: device-resident timed region, serialised roofline pass, optional end-to-end leg from
+    pinned host rows, optional sustained (>= 2 s back-to-back) leg"""
+    g, torch, dist, rank, world, dev = ctx.g, ctx.torch, ctx.dist, ctx.rank, ctx.world, ctx.local_rank
+    wl = WORKLOADS[name]
+    dims, step = wl["dims"], wl["step"]
+    strong = wl["scaling"] == "strong"
+    B = wl["batch"] // world if strong else wl["batch"]        # rows per GPU per step
+    gB = B * world
+    prec_name = "tf32" if tf32 else "bf16"
+
+    def make_net():
+        return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME,
+                                              precision=g.capi.PREC_TF32 if tf32 else g.capi.PREC_BF16,
+                                              flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX, device=dev)
+
+    net = make_net()
+    if world > 1:
+        try:
+            g.dp.init_comm(net, dist, rank, world)
+        except RuntimeError as e:
+            # the in-switch exchange could not be set up (raised on every rank alike, dp._agree): its arena has
+            # already moved, so start over with plain peer memory
+            sys.stderr.write("[bench] %s -- falling back to B2NN_DP=p2p\n" % e)
+            net.close()
+            os.environ["B2NN_DP"] = "p2p"
+            net = make_net()
+            g.dp.init_comm(net, dist, rank, world)
+    net.setStream(ctx.stream.cuda_stream)
+    res = {"workload": name + ": " + (wl["desc"].replace("BF16", "TF32") if tf32 else wl["desc"]), "dims": dims,
+           "dtype": prec_name, "batch_per_gpu": B, "global_batch": gB, "scaling": wl["scaling"],
+           "exchange": net.commMode()}
+
+    if world > 1 and want_dp_check:
+        res["dp_check"] = dp_check(ctx, net, make_net, dims, B, step)
+
+    rows = (16 if name == "c4" else 2) * B
+    x, labels = synth_data(rows, dims[0], dims[-1], 1 + rank, np.float32)
+    ds_dev = g.Dataset(net, x, labels=labels, location=g.capi.DATA_DEVICE)
+    smp = g.Sampler(rows, seed=1)
+    idx_warm = smp.draw(max(W, 1), B)
+    idx_time = smp.draw(K, B)
+
+    # ---- device-resident timed region -----------------------------------------------------
+    train_call(g, net, ds_dev, idx_warm, B, step)
+    ctx.barrier()
+    l0 = net.kernelLaunches()
+    ev0, ev1 = ctx.events()
+    ctx.sampler.begin()
+    ev0.record(ctx.stream)
+    train_call(g, net, ds_dev, idx_time, B, step)
+    ev1.record(ctx.stream)
+    ctx.barrier()
+    ctx.sampler.end(name)
+    ms = ctx.max_over_ranks(ev0.elapsed_time(ev1))
+    res["gpu_launches"] = net.kernelLaunches() - l0
+    res["ms_per_step"] = ms / K
+    res["value"] = gB * K / (ms * 1e-3)
+    res["steps"] = K
+    fl_step_gpu = float(B * flops_per_sample(dims))
+    res["step_tflops_per_gpu"] = fl_step_gpu * K / (ms * 1e-3) / 1e12
+
+    # ---- roofline pass: same K steps with event pairs around every launch, side-stream work serialised -----------
+    net.profileEnable(True)
+    ctx.sampler.begin()
+    ev2, ev3 = ctx.events()
+    ev2.record(ctx.stream)
+    train_call(g, net, ds_dev, idx_time, B, step)
+    ev3.record(ctx.stream)
+    gemm_ms, gemm_n, gemm_flops = net.profileRead()
+    classes = net.profileReadClasses()
+    ctx.sampler.end(name + ":roofline")
+    net.profileEnable(False)
+    prof_step_ms = ev2.elapsed_time(ev3) / K
+    pk = measured_peaks(tf32)
+    achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
+    # a timed region shorter than ~1 s runs at boost clocks (burst peak); longer ones meet the 1 kW cap (sustained peak)
+    region_s = ms * 1e-3
+    which = "burst" if region_s < 1.0 else "sustained"
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        with open(tp) as f:
+            traffic = json.load(f).get(name + ("_tf32" if tf32 else ""))
+    gemm_us = gemm_ms / K * 1e3
+    res["roofline"] = {
+        "bound": "tensor", "kernel": "gemm_%s_pair_kernel (tcgen05 cta_group::2, all epilogues)" % prec_name,
+        "achieved": achieved, "peak": pk[which], "unit": "TFLOP/s", "frac": achieved / pk[which],
+        "peak_kind": "%s (timed region %.3f s)" % (which, region_s), "frac_burst": achieved / pk["burst"],
+        "frac_sustained": achieved / pk["sustained"], "peak_burst": pk["burst"], "peak_sustained": pk["sustained"],
+        "peak_source": pk["src"], "traffic": traffic, "launches": gemm_n, "avg_launch_ms": gemm_ms / max(gemm_n, 1),
+        "flops_per_step": fl_step_gpu, "gemm_share_of_step": (gemm_ms / K) / prof_step_ms,
+        "serialised_step_ms": prof_step_ms, "step_frac_burst": res["step_tflops_per_gpu"] / pk["burst"],
+        "step_frac_sustained": res["step_tflops_per_gpu"] / pk["sustained"],
+        # where the rest of the step goes: each kernel class timed alone in the serialised pass (us per step), and
+        # what the overlapped step spends beyond its contractions
+        "non_gemm_us": {"output_delta": classes["output"][0] / K * 1e3,
+                        "update_or_exchange_side_stream": classes["update"][0] / K * 1e3,
+                        "input_prologue_copy_stream": classes["prologue"][0] / K * 1e3,
+                        "contractions_alone": gemm_us,
+                        "step_minus_contractions_alone": res["ms_per_step"] * 1e3 - gemm_us},
+    }
+
+    # ---- end to end: rows stay in pinned host memory, every step's batch crosses PCIe, per-step loss read back -------
+    if want_e2e:
+        if e2e_rows == "u8":
+            x_host = np.minimum(np.floor(x * 256.0), 255.0).astype(np.uint8)   # IDX pixel bytes, (raw & 0xff) / 255.0 (M:97)
+        elif tf32:
+            x_host = x                                                          # FP32 rows: the operand container of this mode
+        else:
+            u = x.view(np.uint32)                                               # BF16 bits, rounded to nearest even once at staging
+            x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+        x_host_bytes = B * dims[0] * x_host.dtype.itemsize
+        ds_e2e = g.Dataset(net, x_host, labels=labels, location=g.capi.DATA_HOST_PINNED)
+        train_call(g, net, ds_e2e, idx_warm[:min(3, idx_warm.shape[0])], B, step, want_loss=True)
+        ctx.barrier()
+        ctx.sampler.begin()
+        t0 = time.perf_counter()
+        losses = train_call(g, net, ds_e2e, idx_time, B, step, want_loss=True)
+        torch.cuda.synchronize()
+        e2e_s = ctx.max_over_ranks(time.perf_counter() - t0)
+        ctx.sampler.end(name + ":e2e")
+        ctx.barrier()
+        res["e2e"] = {"value": gB * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": x_host_bytes + B * 4,
+                      "d2h_bytes_per_step": 8, "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]),
+                      "rows": "u8" if e2e_rows == "u8" else "f32" if tf32 else "bf16",
+                      "path": "b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset: every step's batch rows are "
+                              "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
+                              "(double-buffered under the previous step's GEMMs); per-step loss read back"}
+        ds_e2e.close()
+
+    # ---- sustained leg (last: it heats the part up): the same call back to back for >= 2 s, power-capped clocks ------
+    if want_sustained:
+        train_call(g, net, ds_dev, idx_time, B, step)
+        ctx.barrier()
+        ev4, ev5 = ctx.events()
+        ctx.sampler.begin()
+        t0 = time.perf_counter()
+        ev4.record(ctx.stream)
+        calls = 0
+        while time.perf_counter() - t0 < 2.0 or calls < 2:
+            for _ in range(4):
+                train_call(g, net, ds_dev, idx_time, B, step)
+            calls += 4
+            torch.cuda.synchronize()
+        ev5.record(ctx.stream)
+        ctx.barrier()
+        ctx.sampler.end(name + ":sustained")
+        sms = ctx.max_over_ranks(ev4.elapsed_time(ev5)) / (calls * K)
+        stf = fl_step_gpu / (sms * 1e-3) / 1e12
+        res["sustained"] = {"ms_per_step": sms, "steps": calls * K, "value": gB / (sms * 1e-3), "tflops_per_gpu": stf,
+                            "step_frac_sustained": stf / pk["sustained"], "clock_tag": name + ":sustained"}
+    ds_dev.close()
+    net.close()
+    return res
+
+
+def measure_f64(ctx, name, K, W, x=None, labels=None, want_cpu=False):
+    """one tiny FP64 parity workload through K1 (f64::fused_train_kernel): device-resident run of K steps in one launch,
+    the per-phase cycle counters of a second, profiled run, and the drop-in per-call path (NeuralNet.gradientStep with
+    host double[B][784] in, synchronous) in microseconds per call"""
+    g, torch, dev = ctx.g, ctx.torch, ctx.local_rank
+    wl = WORKLOADS[name]
+    dims, B, step = wl["dims"], wl["batch"], wl["step"]
+    if wl.get("general"):
+        net = g.GeneralNeuralNet(dims, g.SIGMOID, g.SIGMOID_PRIME, g.SIGMOID, g.SIGMOID_PRIME,
+                                 g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, device=dev)
+    else:
+        net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=dev)
+    net.setStream(ctx.stream.cuda_stream)
+    if x is None:
+        x, labels = synth_data(60000, dims[0], dims[-1], 1 + ctx.rank, np.float64)
+    ds = g.Dataset(net, x, labels=labels)
+    smp = g.Sampler(x.shape[0], seed=1)
+    train_call(g, net, ds, smp.draw(max(W, 1), B), B, step)
+    ctx.barrier()
+    idx = smp.draw(K, B)
+    l0 = net.kernelLaunches()
+    e0, e1 = ctx.events()
+    ctx.sampler.begin()
+    e0.record(ctx.stream)
+    train_call(g, net, ds, idx, B, step)
+    e1.record(ctx.stream)
+    ctx.barrier()
+    ctx.sampler.end(name)
+    ms = ctx.max_over_ranks(e0.elapsed_time(e1))
+    launches = net.kernelLaunches() - l0
+    res = {"workload": name + ": " + wl["desc"], "dims": dims, "dtype": "f64", "batch_per_gpu": B, "global_batch": B,
+           "scaling": "replicas", "value": B * K / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / K,
+           "us_per_step": ms / K * 1e3, "steps": K, "gpu_launches": launches}
+
+    # e2e = the same fast path with the per-step loss read back (the dataset is device-resident like the reference's
+    # in-memory HashMap; index lists cross PCIe every call)
+    ctx.sampler.begin()
+    t0 = time.perf_counter()
+    losses = train_call(g, net, ds, idx, B, step, want_loss=True)
+    torch.cuda.synchronize()
+    e2e_s = ctx.max_over_ranks(time.perf_counter() - t0)
+    ctx.sampler.end(name + ":e2e")
+    # the drop-in call the Java API makes per step (T:70, T:89): NeuralNet.gradientStep with host rows, synchronous
+    nb = 300
+    xb = np.ascontiguousarray(x[:B * 8].reshape(8, B, dims[0]))
+    tb = np.zeros((8, B, dims[-1]))
+    for q in range(8):
+        tb[q, np.arange(B), labels[q * B:(q + 1) * B]] = 1.0
+    dp = C.POINTER(C.c_double)
+    xp = [xb[q].ctypes.data_as(dp) for q in range(8)]
+    tp = [tb[q].ctypes.data_as(dp) for q in range(8)]
+    fn, h = g.capi.lib().b2nn_gradient_step, net._h
+    for q in range(20):
+        g.capi.check(fn(h, xp[q % 8], tp[q % 8], B, step, 0.9, 0, None))
+    t1 = time.perf_counter()
+    for q in range(nb):
+        fn(h, xp[q % 8], tp[q % 8], B, step, 0.9, 0, None)
+    per_call_us = (time.perf_counter() - t1) / nb * 1e6
+    res["e2e"] = {"value": B * K / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": 8,
+                  "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]), "rows": "f64",
+                  "path": "b2nn_train_indexed over the device-resident dataMaster; index lists cross PCIe every call, "
+                          "per-step loss read back",
+                  "gradient_step_call": {"us_per_call": per_call_us, "value": B / (per_call_us * 1e-6), "unit": "samples/s",
+                                         "h2d_bytes_per_call": B * (dims[0] + dims[-1]) * 8, "calls": nb,
+                                         "path": "b2nn_gradient_step (NeuralNet.gradientStep, S:297): host double rows "
+                                                 "and targets in, one K1 step, stream sync before return"}}
+
+    # K1 phase counters (cycles per step on CTA 0): the latency chain this kernel is bound by
+    net.k1Profile(True)
+    kp = min(K, 2000)
+    train_call(g, net, ds, idx[:kp], B, step)
+    net.sync()
+    phases, nsteps = net.k1Profile(False)
+    total = sum(phases.values())
+    P = n_weights(dims)
+    fl = float(B * flops_per_sample(dims))
+    res["roofline"] = {
+        "bound": "latency", "kernel": "f64::fused_train_kernel (K1: one persistent cooperative launch for the whole run)",
+        "achieved": ms / K * 1e3, "unit": "us/step", "peak": None, "frac": None, "traffic": None,
+        "why_no_peak": "the state (%.1f MB of FP64 weights + velocity) never leaves the chip and a step is %.1f MFLOP: "
+                       "neither HBM nor the tensor pipe bounds it, the chain of dependent phases and its grid barriers does"
+                       % (P * 16 / 1e6, fl / 1e6),
+        "phase_cycles_per_step": phases, "cycles_per_step": total, "profiled_steps": nsteps,
+        "barrier_share": (phases.get("barrier1", 0) + phases.get("barrier2", 0)) / total if total else None,
+        "fp64_gflops": fl / (ms / K * 1e-3) / 1e9, "flops_per_step": fl,
+        "l2_resident_bytes_per_step": 4 * P * 8 + B * (dims[0] + dims[-1]) * 8}
+    if want_cpu:
+        res["cpu_baseline"] = cpu_baseline_block(name)
+    ds.close()
+    net.close()
+    return res
 
 
 def run_b2nn(args):
@@ -213,227 +572,80 @@ def run_b2nn(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     g = ge.load_package()
     wl = WORKLOADS[args.workload]
-    dims, B = wl["dims"], wl["batch"]
     K, W = args.steps, args.warmup
-    bf16 = wl["prec"] == "bf16"                      # a tensor-core ("wide") workload
-    tf32 = bf16 and args.precision == "tf32"         # ... computed with TF32 operands instead of BF16
-    prec_name = "tf32" if tf32 else wl["prec"]
+    wide = wl["prec"] == "bf16"
+    tf32 = wide and args.precision == "tf32"
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ctx = Ctx(g, torch, dist, rank, world, local_rank, sampler)
 
-    sampler_thread = ClockSampler(local_rank)
-    sampler_thread.start()
-
-    def make_net():
-        if bf16:
-            return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME,
-                                                  precision=g.capi.PREC_TF32 if tf32 else g.capi.PREC_BF16,
-                                                  flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX,
-                                                  device=local_rank)
-        if wl.get("general"):
-            return g.GeneralNeuralNet(dims, g.SIGMOID, g.SIGMOID_PRIME, g.SIGMOID, g.SIGMOID_PRIME,
-                                      g.HALF_SQUARED_ERROR, g.HALF_SQUARED_ERROR_PRIME, device=local_rank)
-        return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=local_rank)
-
-    net = make_net()
-    if world > 1 and bf16:   # the tiny FP64 configs do not shard: N independent replicas, no exchange
-        try:
-            g.dp.init_comm(net, dist, rank, world)
-        except RuntimeError as e:
-            # the in-switch exchange could not be set up (raised on every rank alike, dp._agree): its arena has
-            # already moved, so start over with plain peer memory
-            sys.stderr.write("[bench] %s -- falling back to B2NN_DP=p2p\n" % e)
-            net.close()
-            os.environ["B2NN_DP"] = "p2p"
-            net = make_net()
-            g.dp.init_comm(net, dist, rank, world)
-    stream = torch.cuda.current_stream()
-    net.setStream(stream.cuda_stream)
-
-    rows = 16 * B if bf16 else 60000
-    x, labels = synth_data(rows, dims[0], dims[-1], 1 + rank, np.float32 if bf16 else np.float64)
-    ds_dev = g.Dataset(net, x, labels=labels, location=g.capi.DATA_DEVICE)
-    smp = g.Sampler(rows, seed=1)
-    idx_warm = smp.draw(max(W, 1), B)
-    idx_time = smp.draw(K, B)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def train(ds, idx, want_loss=False):
-        import ctypes as C
-        loss = np.empty(idx.shape[0]) if want_loss else None
-        g.capi.check(g.capi.lib().b2nn_train_indexed(
-            net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), idx.shape[0], B, wl["step"], 0.9,
-            loss.ctypes.data_as(C.POINTER(C.c_double)) if want_loss else None))
-        return loss
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---- device-resident timed region -----------------------------------------------------
-    train(ds_dev, idx_warm)
-    barrier()
-    l0 = net.kernelLaunches()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler_thread.begin()
-    ev0.record(stream)
-    train(ds_dev, idx_time)
-    ev1.record(stream)
-    barrier()
-    sampler_thread.end()
-    ms = max_over_ranks(ev0.elapsed_time(ev1))
-    launches = net.kernelLaunches() - l0
-    value = world * B * K / (ms * 1e-3)
-
-    # ---- roofline pass: same K steps with event pairs around every contraction launch ------
-    roof = None
-    if bf16:
-        net.profileEnable(True)   # side-stream work is serialised in this pass: each contraction is timed alone
-        sampler_thread.begin()
-        ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev2.record(stream)
-        train(ds_dev, idx_time)
-        ev3.record(stream)
-        gemm_ms, gemm_n, gemm_flops = net.profileRead()
-        sampler_thread.end()
-        net.profileEnable(False)
-        prof_step_ms = ev2.elapsed_time(ev3) / K
-        pk = measured_peaks()
-        if tf32:
-            # MEASURED_PEAKS.json holds no TF32 figure: the profiling recipe's nominal dense TF32 peak stands in
-            pk = dict(pk, tflops=1100.0, src="nominal dense TF32 peak (B200_PROFILING.md); no measured TF32 peak on file")
-            tpk = os.path.join(ROOT, "profiles", "tf32_peaks.json")   # written by scratch/tf32_peak.py on the GPU box
-            if os.path.exists(tpk):
-                with open(tpk) as f:
-                    pk = dict(pk, tflops=float(json.load(f)["tf32_tflops_sustained"]),
-                              src="measured (profiles/tf32_peaks.json: torch.matmul fp32 allow_tf32 8192^3, sustained)")
-        achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            with open(tp) as f:
-                traffic = json.load(f).get(args.workload + ("_tf32" if tf32 else ""))
-        roof = {"bound": "tensor", "kernel": "gemm_%s_pair_kernel (tcgen05 cta_group::2, all epilogues)" % prec_name, "achieved": achieved,
-                "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "peak_source": pk["src"],
-                "traffic": traffic, "launches": gemm_n, "avg_launch_ms": gemm_ms / max(gemm_n, 1),
-                "flops_per_step": float(B * flops_per_sample(dims)),
-                "gemm_share_of_step": (gemm_ms / K) / prof_step_ms, "serialised_step_ms": prof_step_ms,
-                "step_tflops": world * B * flops_per_sample(dims) * K / (ms * 1e-3) / 1e12 / world}
+    also = {}
+    if wide:
+        main = measure_wide(ctx, args.workload, tf32, K, W, want_e2e=True, want_sustained=not args.no_sustained,
+                            e2e_rows=args.e2e_rows)
+        if not args.no_also:
+            if args.workload != "c5":
+                # BASELINE configs[4] at every N: strong scaling of the 8192-wide net over a global batch of 32768
+                try:
+                    also["c5"] = measure_wide(ctx, "c5", False, 5, 3, want_e2e=False, want_sustained=False,
+                                              want_dp_check=False)
+                except Exception as e:  # noqa
+                    also["c5"] = {"error": repr(e)}
+            if world == 1 and args.workload == "c4" and not tf32:
+                try:
+                    also["c4_tf32"] = measure_wide(ctx, "c4", True, 20, 5, want_e2e=False, want_sustained=False)
+                except Exception as e:  # noqa
+                    also["c4_tf32"] = {"error": repr(e)}
+                try:
+                    x64, l64 = synth_data(60000, 784, 10, 1, np.float64)
+                    also["c2"] = measure_f64(ctx, "c2", 20000, 200, x64, l64, want_cpu=not args.no_cpu)
+                    also["c1"] = measure_f64(ctx, "c1", 20000, 200, x64, l64)
+                    also["c3"] = measure_f64(ctx, "c3", 20000, 200, x64, l64)
+                except Exception as e:  # noqa
+                    also["f64_error"] = repr(e)
     else:
-        pk = measured_peaks()
-        P = n_weights(dims)
-        bytes_step = 4 * P * 8 + B * (dims[0] + dims[-1]) * 8   # r+w of W and V + batch rows (L2-resident)
-        achieved = bytes_step * K / (ms * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "f64 step kernels (latency-bound; state is L2-resident)", "achieved": achieved,
-                "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"], "peak_source": pk["src"],
-                "traffic": None}
-
-    # ---- end to end: rows stay in pinned host memory, every step's batch crosses PCIe, per-step loss read back
-    if bf16:
-        # host rows in the operand precision of this mode (BF16 bits, rounded to nearest even once at staging time,
-        # like the reference's one-off (byte & 0xff) / 255.0 at load, MNISTTrainer.java:97)
-        if args.e2e_rows == "u8":
-            # rows in the reference's own storage format, IDX pixel bytes read as (raw & 0xff) / 255.0 (M:97)
-            x_host = np.minimum(np.floor(x * 256.0), 255.0).astype(np.uint8)
-        elif tf32:
-            x_host = x                                   # FP32 rows: the operand container of this mode
-        else:
-            u = x.view(np.uint32)
-            x_host = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
-        x_host_bytes = B * dims[0] * x_host.dtype.itemsize
-        ds_e2e = g.Dataset(net, x_host, labels=labels, location=g.capi.DATA_HOST_PINNED)
-    else:
-        x_host_bytes = 0
-        ds_e2e = ds_dev
-    train(ds_e2e, idx_warm[:min(3, idx_warm.shape[0])], want_loss=True)
-    barrier()
-    sampler_thread.begin()
-    t0 = time.perf_counter()
-    losses = train(ds_e2e, idx_time, want_loss=True)
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    sampler_thread.end()
-    barrier()
-    e2e = {"value": world * B * K / e2e_s, "unit": "samples/s",
-           "h2d_bytes_per_step": (x_host_bytes if bf16 else 0) + B * 4, "d2h_bytes_per_step": 8,
-           "ms_per_step": e2e_s / K * 1e3, "last_loss": float(losses[-1]),
-           "rows": ("u8" if args.e2e_rows == "u8" else "f32" if tf32 else "bf16") if bf16 else "f64",
-           "path": ("b2nn_train_indexed over a B2NN_DATA_HOST_PINNED dataset of BF16 (or, with --e2e-rows u8, pixel-byte) rows: every step's batch rows are "
-                    "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
-                    "(double-buffered under the previous step's GEMMs); per-step loss read back" if bf16 else
-                    "b2nn_train_indexed over the device-resident dataMaster (784-wide rows live on the GPU like "
-                    "the reference's in-memory HashMap); index lists cross PCIe every call")}
-
-    # ---- the other headline config, quoted beside the main one --------------------------------
-    also = None
-    if args.workload == "c4" and world == 1 and not args.no_also:
-        try:
-            also = tiny_config_line(g, torch, local_rank)
-        except Exception as e:  # noqa
-            also = {"error": repr(e)}
+        main = measure_f64(ctx, args.workload, K, W)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cs, cw = {"c4": (10, 1), "c5": (3, 1), "c2": (500, 20), "c1": (3000, 50), "c3": (1500, 50)}[args.workload]   # ~10-15 s of CPU work each
-        val, dt, r = cpu_reference_run(args.workload, cs, cw)
-        cpu = {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
-               "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" %
-                         (cs, r, dt)}
+        cpu = cpu_baseline_block(args.workload)
 
     if rank == 0:
+        dims = wl["dims"]
+        if wide:
+            par = "dp%d" % world
+            l2 = ("no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh batch, larger than "
+                  "the 126 MB L2" % (n_weights(dims) * 12 / 1e6))
+            scaling = wl["scaling"]
+        else:
+            # the tiny FP64 configs do not shard: every rank is an independent replica with no exchange;
+            # `value` is ONE replica's rate (max step time over the replicas), the replica count is stated beside it
+            par = "replicas only x%d (no exchange; value = one replica's rate)" % world
+            l2 = ("state is L2-resident by design (%.1f MB of weights + velocity); batches cycle through 60000 rows "
+                  "(376 MB)" % (n_weights(dims) * 16 / 1e6))
+            scaling = "weak"
+        if "sustained" in main:
+            clk = sampler.summary({main["sustained"].pop("clock_tag")})
+            main["sustained"]["sm_mhz"], main["sustained"]["reasons"] = clk.get("sm_mhz"), clk.get("reasons")
         out = {
-            "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K,
-            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": prec_name, "data": "synthetic",
-            "config": {"workload": args.workload + ": " + (wl["desc"].replace("BF16", "TF32") if tf32 else wl["desc"]),
-                       "dims": dims, "batch_per_gpu": B,
-                       "global_batch": B * world,
-                       "parallelism": "dp%d" % world if bf16 else "replicas only x%d (no exchange)" % world,
-                       "exchange": net.commMode() if bf16 else "single",
-                       "l2": "no flush needed: each step streams %.0f MB of weight/velocity state plus a fresh "
-                             "batch, larger than the 126 MB L2" % (n_weights(dims) * 12 / 1e6) if bf16 else
-                             "state is L2-resident by design (%.1f MB of weights + velocity); batches cycle through "
-                             "60000 rows (376 MB)" % (n_weights(dims) * 16 / 1e6)},
-            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
-            "clocks": sampler_thread.summary(),
+            "metric": "train_samples_per_sec", "value": main["value"], "unit": "samples/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": scaling,
+            "vs_baseline": None, "dtype": main["dtype"], "data": "synthetic",
+            "config": {"workload": main["workload"], "dims": dims, "batch_per_gpu": main["batch_per_gpu"],
+                       "global_batch": main["global_batch"], "parallelism": par,
+                       "exchange": main.get("exchange", "single"), "replicas": world if not wide else None, "l2": l2},
+            "roofline": main["roofline"], "cpu_baseline": cpu, "e2e": main["e2e"],
+            "gpu_launches": main["gpu_launches"],
+            "clocks": sampler.summary({args.workload, args.workload + ":roofline", args.workload + ":e2e"}),
         }
+        for k in ("sustained", "dp_check", "step_tflops_per_gpu"):
+            if k in main:
+                out[k] = main[k]
         if also:
             out["also"] = also
         emit(out)
     if world > 1:
         dist.destroy_process_group()
-
-
-def tiny_config_line(g, torch, device):
-    """BASELINE configs[1]: 784-300-100-10 FP64 parity mode, batch 16 (quoted beside the wide config)"""
-    dims, B, iters = [784, 300, 100, 10], 16, 2000
-    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=device)
-    stream = torch.cuda.current_stream()
-    net.setStream(stream.cuda_stream)
-    x, labels = synth_data(60000, 784, 10, 1, np.float64)
-    ds = g.Dataset(net, x, labels=labels)
-    smp = g.Sampler(60000, seed=1)
-    import ctypes as C
-
-    def run(idx):
-        g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)),
-                                                     idx.shape[0], B, 0.0125, 0.9, None))
-    run(smp.draw(200, B))
-    torch.cuda.synchronize()
-    idx = smp.draw(iters, B)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    run(idx)
-    e1.record(stream)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    return {"workload": "c2: " + WORKLOADS["c2"]["desc"], "value": iters * B / (ms * 1e-3), "unit": "samples/s",
-            "us_per_step": ms / iters * 1e3, "dtype": "f64", "steps": iters}
 
 
 def main():
@@ -452,9 +664,10 @@ def main():
     ap.add_argument("--e2e-rows", default="bf16", choices=["bf16", "u8"],
                     help="element type of the pinned host rows of the e2e leg (u8 = IDX pixel bytes / 255)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
-                    help="operand type of the tensor-core workloads c4 / c5 (tf32 at N > 1 uses the NCCL exchange)")
+                    help="operand type of the tensor-core workloads c4 / c5")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-also", action="store_true", help="skip the 784-300-100-10 side measurement")
+    ap.add_argument("--no-also", action="store_true", help="skip the side measurements (c5, TF32, the FP64 configs)")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s back-to-back leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
