@@ -73,7 +73,7 @@ def test_weights_roundtrip_and_init(g, orc):
     assert np.array_equal(net.getWeights(), v.astype(np.float32).astype(np.float64))
 
 
-def emulate_bf16_step(dims, w0, x, lab, step, alpha=0.01):
+def emulate_bf16_step(dims, w0, x, lab, step, alpha=0.01, act="leaky"):
     """numpy model of the BF16 path: operands rounded to bfloat16 exactly where the kernels round
     them (a_l, delta_l, the two BF16 weight copies), products accumulated in FP64 (the kernels
     accumulate in FP32), FP32 master update.  Returns (mean loss, update v = step*G/B per layer)."""
@@ -84,7 +84,10 @@ def emulate_bf16_step(dims, w0, x, lab, step, alpha=0.01):
         n = dims[l] * dims[l + 1]
         W.append(w0[off:off + n].reshape(dims[l], dims[l + 1]))
         off += n
-    leaky = lambda z: np.where(z > 0, z, alpha * z)
+    if act == "sigmoid":   # smooth: no slope flips (f' from the stored activation)
+        leaky, fprime = (lambda z: 1.0 / (1.0 + np.exp(-z))), (lambda a: a * (1.0 - a))
+    else:
+        leaky, fprime = (lambda z: np.where(z > 0, z, alpha * z)), (lambda a: np.where(a > 0, 1.0, alpha))
     a = [bf16_round(leaky(x.astype(np.float32).astype(np.float64)))]
     for l in range(L - 1):
         a.append(bf16_round(leaky(a[l] @ bf16_round(W[l]))))
@@ -98,7 +101,7 @@ def emulate_bf16_step(dims, w0, x, lab, step, alpha=0.01):
     d = [None] * (L + 1)
     d[L] = bf16_round(p - t)
     for l in range(L - 1, 0, -1):
-        d[l] = bf16_round((d[l + 1] @ bf16_round(W[l]).T) * np.where(a[l] > 0, 1.0, alpha))
+        d[l] = bf16_round((d[l + 1] @ bf16_round(W[l]).T) * fprime(a[l]))
     return loss, [step * (a[l].T @ d[l + 1]) / B for l in range(L)]
 
 

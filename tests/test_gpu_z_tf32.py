@@ -70,7 +70,7 @@ def test_tf32_weights_roundtrip(g):
     assert np.array_equal(net.getVelocity(), np.zeros(net.numWeights))
 
 
-def emulate_tf32_step(dims, w0, x, lab, step, alpha=0.01):
+def emulate_tf32_step(dims, w0, x, lab, step, alpha=0.01, act="leaky"):
     """numpy model of the TF32 path: FP32 arrays in memory, every GEMM operand rounded to TF32 on its way into the
     tensor core, products accumulated in FP64 (the kernels accumulate in FP32).  Returns (mean loss, update
     v = step*G/B per layer)."""
@@ -82,7 +82,10 @@ def emulate_tf32_step(dims, w0, x, lab, step, alpha=0.01):
         n = dims[l] * dims[l + 1]
         W.append(w0[off:off + n].reshape(dims[l], dims[l + 1]))
         off += n
-    leaky = lambda z: np.where(z > 0, z, alpha * z)
+    if act == "sigmoid":   # smooth: no slope flips (f' from the stored activation)
+        leaky, fprime = (lambda z: 1.0 / (1.0 + np.exp(-z))), (lambda a: a * (1.0 - a))
+    else:
+        leaky, fprime = (lambda z: np.where(z > 0, z, alpha * z)), (lambda a: np.where(a > 0, 1.0, alpha))
     a = [f32(leaky(f32(x)))]
     for l in range(L - 1):
         a.append(f32(leaky(tf32_round(a[l]) @ tf32_round(W[l]))))
@@ -96,7 +99,7 @@ def emulate_tf32_step(dims, w0, x, lab, step, alpha=0.01):
     d = [None] * (L + 1)
     d[L] = f32(p - t)
     for l in range(L - 1, 0, -1):
-        d[l] = f32((tf32_round(d[l + 1]) @ tf32_round(W[l]).T) * np.where(a[l] > 0, 1.0, alpha))
+        d[l] = f32((tf32_round(d[l + 1]) @ tf32_round(W[l]).T) * fprime(a[l]))
     return loss, [step * (tf32_round(a[l]).T @ tf32_round(d[l + 1])) / B for l in range(L)]
 
 
@@ -210,10 +213,12 @@ def test_tf32_pixel_byte_rows_match_float_rows(g):
     assert da.evaluate()[0] == db.evaluate()[0]
 
 
-def test_tf32_peer_memory_exchange_is_refused(g):
-    """TF32 nets exchange gradients through NCCL only: the fused peer-memory / multicast kernel replicates a BF16
-    operand copy they do not have (dp.init_comm picks the NCCL exchange for them)"""
+def test_tf32_peer_memory_export_without_communicator(g):
+    """TF32 nets take the fused peer-memory / multicast exchange too (the kernel replicates their FP32 weights instead
+    of a BF16 copy; 2-GPU parity in tests/test_dp.py): the CUDA IPC handle of the arena exports, the multicast export
+    still needs a communicator (world > 1) and says so without touching the net"""
     net = tf32_net(g, [64, 32, 8])
-    with pytest.raises(NotImplementedError):
-        net.commIpcExport()
+    assert len(net.commIpcExport()) == 64
     assert net.commNvlsExport() is None
+    w = net.getWeights()
+    assert np.isfinite(w).all() and w.size == net.numWeights

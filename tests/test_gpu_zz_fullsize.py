@@ -93,44 +93,75 @@ def test_bare_delta_contraction_full_size(g, prec):
     v = net.getVelocity()
     d1 = v[:n * n].reshape(n, n) * n
     ref = -(t @ W1.T)
-    # BF16 nets store D_1 rounded to BF16 (relative 2^-9), TF32 nets keep FP32
-    slack = 2.0 ** -8 * np.abs(ref) if prec == "bf16" else 0.0
+    # D_1 reaches the velocity through the layer-0 gradient contraction, which reads it as an operand: BF16 nets store it
+    # rounded to BF16 (relative 2^-9), TF32 nets store FP32 but TMA rounds it to TF32 (relative 2^-11) on the way in
+    slack = (2.0 ** -8 if prec == "bf16" else 2.0 ** -10) * np.abs(ref)
     assert np.all(np.abs(d1 - ref) <= BARE_TOL[prec] * np.abs(ref).max() + slack), np.abs(d1 - ref).max()
     assert not v[n * n:].any()                                              # a_1 = 0: no gradient for W_1
 
 
+def report(line):
+    """measured errors, kept when B2NN_TEST_REPORT names a file (profiles/r02_fullsize_parity_report.txt)"""
+    import os
+    if os.environ.get("B2NN_TEST_REPORT"):
+        with open(os.environ["B2NN_TEST_REPORT"], "a") as f:
+            f.write(line + "\n")
+
+
+# Per-layer bound of one step against the rounding model.  With a SMOOTH activation (sigmoid) the model and the kernels
+# differ only by FP32 accumulation order and 1-ulp effects: 1e-2 (BF16) / 1e-3 (TF32) in every layer, the bounds of the
+# small-size tests (measured at C4 size: <= 4.9e-4 / <= 9e-5).  With leaky-ReLU a unit whose pre-activation lies within
+# the FP32 accumulation noise of zero takes the other slope in one of the two computations: its delta is off by ~100 %,
+# and every gradient BELOW it inherits the difference (Frobenius ~ sqrt(fraction of flipped units); measured at C4 size:
+# 4.1e-3 BF16, 3.4e-3 TF32 -- the same in both precisions, as a flip count should be); the top layer has no f' above it
+# and keeps the tight bound (measured 3.4e-4 / 1.2e-4).  Measured values: profiles/r02_fullsize_parity_report.txt.
+STEP_TOL = {("bf16", "sigmoid"): (1e-2, 1e-2), ("tf32", "sigmoid"): (1e-3, 1e-3),
+            ("bf16", "leaky"): (1e-2, 1e-2), ("tf32", "leaky"): (1e-3, 1e-2)}   # (top layer, layers below)
+
+
+def check_step_vs_model(tag, prec, act, dims, v, emu_v, lower_tol_scale=1.0):
+    top, lower = STEP_TOL[(prec, act)]
+    L, off = len(dims) - 1, 0
+    for l in range(L):
+        n = dims[l] * dims[l + 1]
+        a, e = v[off:off + n], emu_v[l].ravel()
+        rel = np.linalg.norm(a - e) / np.linalg.norm(e)
+        report("%s %s %s layer %d rel %.3g" % (tag, prec, act, l, rel))
+        assert rel <= (top if l == L - 1 else lower * lower_tol_scale), (tag, prec, act, l, rel)
+        off += n
+
+
+@pytest.mark.parametrize("act", ["sigmoid", "leaky"])
 @pytest.mark.parametrize("prec", ["bf16", "tf32"])
-def test_c4_full_step_vs_rounding_model(g, prec):
-    """one gradientStep of the real C4 against the numpy model that rounds where the kernels round, evaluated at full
-    size: per-layer update within 1e-2 (BF16) / 1e-3 (TF32) Frobenius, batch loss within 1e-3 / 1e-4"""
-    tol, ltol, emu = {"bf16": (1e-2, 1e-3, emulate_bf16_step), "tf32": (1e-3, 1e-4, emulate_tf32_step)}[prec]
+def test_c4_full_step_vs_rounding_model(g, prec, act):
+    """one gradientStep of the real C4 (and of its sigmoid twin, which has no slope discontinuity) against the numpy
+    model that rounds where the kernels round, evaluated at full size; batch loss within 1e-3 (BF16) / 1e-4 (TF32)"""
+    ltol, emu = {"bf16": (1e-3, emulate_bf16_step), "tf32": (1e-4, emulate_tf32_step)}[prec]
     rng = np.random.RandomState(8)
     x = rng.rand(B, DIMS[0]).astype(np.float32)
     lab = rng.randint(0, DIMS[-1], B).astype(np.int32)
-    net = make(g, prec_id(g, prec))
+    f, fp = (g.SIGMOID, g.SIGMOID_PRIME) if act == "sigmoid" else (g.LEAKY_RELU, g.LEAKY_RELU_PRIME)
+    net = g.SoftmaxCrossEntropyNeuralNet(DIMS, f, fp, precision=prec_id(g, prec),
+                                         flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX)
     w0 = net.getWeights()
     loss = net.gradientStepLabeled(x, lab, 0.01, 0.0, returnLoss=True)
     v = net.getVelocity()
     net.close()
-    emu_loss, emu_v = emu(DIMS, w0, x, lab, 0.01)
+    emu_loss, emu_v = emu(DIMS, w0, x, lab, 0.01, act=act)
+    report("c4 %s %s loss rel %.3g" % (prec, act, abs(loss - emu_loss) / max(1.0, abs(emu_loss))))
     assert abs(loss - emu_loss) <= ltol * max(1.0, abs(emu_loss)), (loss, emu_loss)
-    off = 0
-    for l in range(len(DIMS) - 1):
-        n = DIMS[l] * DIMS[l + 1]
-        a, e = v[off:off + n], emu_v[l].ravel()
-        rel = np.linalg.norm(a - e) / np.linalg.norm(e)
-        assert rel <= tol, (prec, l, rel)
-        off += n
+    check_step_vs_model("c4", prec, act, DIMS, v, emu_v)
 
 
 @pytest.mark.parametrize("prec", ["bf16", "tf32"])
 def test_six_matrix_net_vs_oracle(g, orc, prec):
     """BASELINE configs[4]'s shape (7 dims = 6 weight matrices, 1000 classes) at a width the oracle can run: first step
-    against the rounding model (tight) and the FP64 oracle (loose: leaky-ReLU slope flips compound through five hidden
-    layers), then two more momentum steps with the batch loss tracked against the oracle's"""
+    against the rounding model and the FP64 oracle (loose: leaky-ReLU slope flips compound through five hidden layers,
+    see STEP_TOL; twice the C4 allowance below the top layer, measured <= 1e-2), then two more momentum steps with the
+    batch loss tracked against the oracle's.  Measured against the oracle: BF16 <= 7.4e-2 (cosine >= 0.9973), TF32
+    <= 3.1e-2 (cosine >= 0.9995) below the top layer, 5e-3 / 6e-4 in the top layer."""
     dims, Bs = [384] * 6 + [1000], 128
-    tol, otol, cos_min, emu = {"bf16": (1e-2, 2e-1, 0.98, emulate_bf16_step),
-                               "tf32": (1e-3, 5e-2, 0.998, emulate_tf32_step)}[prec]
+    otol, cos_min, emu = {"bf16": (2e-1, 0.98, emulate_bf16_step), "tf32": (5e-2, 0.998, emulate_tf32_step)}[prec]
     net = make(g, prec_id(g, prec), dims)
     ref = orc.OracleNet(dims)
     ref.set_weights(net.getWeights())
@@ -149,12 +180,14 @@ def test_six_matrix_net_vs_oracle(g, orc, prec):
         if it == 0:
             assert abs(loss - emu_loss) <= 1e-3 * max(1.0, abs(emu_loss))
             du, du_ref = w0 - net.getWeights(), w0 - ref.get_weights()
+            check_step_vs_model("six", prec, "leaky", dims, du, emu_v, lower_tol_scale=2.0)
             off = 0
             for l in range(len(dims) - 1):
                 n = dims[l] * dims[l + 1]
-                a, r, e = du[off:off + n], du_ref[off:off + n], emu_v[l].ravel()
-                assert np.linalg.norm(a - e) <= tol * np.linalg.norm(e), (l, np.linalg.norm(a - e) / np.linalg.norm(e))
-                assert np.linalg.norm(a - r) <= otol * np.linalg.norm(r), (l, np.linalg.norm(a - r) / np.linalg.norm(r))
+                a, r = du[off:off + n], du_ref[off:off + n]
+                rel = np.linalg.norm(a - r) / np.linalg.norm(r)
+                report("six %s vs oracle layer %d rel %.3g cos %.6f" % (prec, l, rel, a @ r / np.linalg.norm(a) / np.linalg.norm(r)))
+                assert rel <= otol, (l, rel)
                 assert a @ r >= cos_min * np.linalg.norm(a) * np.linalg.norm(r)
                 off += n
 
