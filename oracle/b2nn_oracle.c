@@ -9,6 +9,7 @@
 #include "b2nn_oracle.h"
 
 #include <math.h>
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -278,8 +279,120 @@ void orc_net_weight_gradient(orc_net *n, const double *x, const double *t, doubl
     free(dnet); free(out);
 }
 
+/* ---- worker threads (test infrastructure convenience, NOT in the reference, which is serial) --------------------
+ * With orc_set_threads(T > 1) the per-sample gradients of a batch (S:305-308) are computed by T threads, each with
+ * its own `neurons` scratch, and then summed IN BATCH ORDER (S:309-317) element by element: every floating-point
+ * operation and its order per element are those of the serial loop, so the result is bit-identical to it (checked in
+ * tests/test_oracle.py).  The timed CPU baseline always runs with 1 thread. */
+static int g_threads = 1;
+void orc_set_threads(int32_t t) { g_threads = t < 1 ? 1 : t; }
+int32_t orc_get_threads(void) { return g_threads; }
+
+/* a shallow copy of the net with private pre-activation scratch (weights are only read by the per-sample pass) */
+static void local_net_init(orc_net *dst, const orc_net *src) {
+    *dst = *src;
+    dst->neurons = (double **)calloc(src->n_dims, sizeof(double *));
+    for (int l = 1; l < src->n_dims; l++) dst->neurons[l] = (double *)calloc(src->dims[l], sizeof(double));
+}
+static void local_net_free(orc_net *n) {
+    for (int l = 1; l < n->n_dims; l++) free(n->neurons[l]);
+    free(n->neurons);
+}
+
+/* static-chunk parallel for over [0, n) on up to nt POSIX threads (the image's gcc has no libgomp) */
+typedef void (*par_fn)(int64_t lo, int64_t hi, void *ctx);
+typedef struct { par_fn fn; void *ctx; int64_t lo, hi; } par_task;
+static void *par_trampoline(void *p) {
+    par_task *t = (par_task *)p;
+    t->fn(t->lo, t->hi, t->ctx);
+    return NULL;
+}
+static void par_for(int64_t n, int nt, par_fn fn, void *ctx) {
+    if (nt > n) nt = (int)n;
+    if (nt <= 1) { fn(0, n, ctx); return; }
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)nt);
+    par_task *tk = (par_task *)malloc(sizeof(par_task) * (size_t)nt);
+    for (int i = 0; i < nt; i++) {
+        tk[i].fn = fn; tk[i].ctx = ctx;
+        tk[i].lo = n * i / nt; tk[i].hi = n * (i + 1) / nt;
+        if (i > 0 && pthread_create(&th[i], NULL, par_trampoline, &tk[i]) != 0) { tk[i].fn(tk[i].lo, tk[i].hi, ctx); tk[i].fn = NULL; }
+    }
+    par_trampoline(&tk[0]);
+    for (int i = 1; i < nt; i++)
+        if (tk[i].fn) pthread_join(th[i], NULL);
+    free(th); free(tk);
+}
+
+typedef struct {
+    orc_net *n; const double *x, *t; double *out; int32_t B; double step, momentum;
+} par_ctx;
+
+static void par_sample_gradients(int64_t lo, int64_t hi, void *p) {
+    par_ctx *c = (par_ctx *)p;
+    int d0 = c->n->dims[0], dl = c->n->dims[c->n->n_dims - 1];
+    orc_net local;
+    local_net_init(&local, c->n);
+    for (int64_t b = lo; b < hi; b++)
+        orc_net_weight_gradient(&local, c->x + b * d0, c->t + b * dl, c->out + b * c->n->n_weights);
+    local_net_free(&local);
+}
+static void par_sum_and_update(int64_t lo, int64_t hi, void *p) {
+    par_ctx *c = (par_ctx *)p;
+    orc_net *n = c->n;
+    const int64_t P = n->n_weights;
+    const int batch_size = c->B;                                            /* batch.size(), S:325 */
+    for (int64_t q = lo; q < hi; q++) {
+        double a = c->out[q];                                               /* S:319: the first sample's map */
+        for (int b = 1; b < c->B; b++) a += c->out[(int64_t)b * P + q];     /* S:309-317, ascending batch order */
+        double adj = c->step * a / batch_size + c->momentum * n->prev[q];   /* S:333 */
+        n->w[q] -= adj;                                                     /* S:338 */
+        n->prev[q] = adj;                                                   /* S:339, S:344 */
+    }
+}
+static void gradient_step_threads(orc_net *n, const double *x, const double *t, int32_t B, double step,
+                                  double momentum) {
+    int64_t P = n->n_weights;
+    par_ctx c = {n, x, t, (double *)malloc(sizeof(double) * (size_t)P * (size_t)B), B, step, momentum};
+    par_for(B, g_threads, par_sample_gradients, &c);
+    par_for(P, g_threads, par_sum_and_update, &c);
+    n->time++;                                                              /* S:343 */
+    free(c.out);
+}
+
+static void par_loss_rows(int64_t lo, int64_t hi, void *p) {
+    par_ctx *c = (par_ctx *)p;
+    int d0 = c->n->dims[0], dl = c->n->dims[c->n->n_dims - 1];
+    orc_net local;
+    local_net_init(&local, c->n);
+    for (int64_t i = lo; i < hi; i++) c->out[i] = orc_net_loss(&local, c->x + i * d0, c->t + i * dl);
+    local_net_free(&local);
+}
+/* per-row loss of rows [0, count) into out[] (rows are independent; callers sum in row order) */
+void orc_net_loss_rows(orc_net *n, const double *x, const double *t, int64_t count, double *out) {
+    par_ctx c = {n, x, t, out, 0, 0.0, 0.0};
+    par_for(count, g_threads, par_loss_rows, &c);
+}
+
+static void par_propagate_rows(int64_t lo, int64_t hi, void *p) {
+    par_ctx *c = (par_ctx *)p;
+    int d0 = c->n->dims[0], dl = c->n->dims[c->n->n_dims - 1];
+    orc_net local;
+    local_net_init(&local, c->n);
+    for (int64_t i = lo; i < hi; i++) orc_net_propagate(&local, c->x + i * d0, c->out + i * dl);
+    local_net_free(&local);
+}
+/* propagate rows [0, count) into y [count][dL] */
+void orc_net_propagate_rows(orc_net *n, const double *x, int64_t count, double *y) {
+    par_ctx c = {n, x, NULL, y, 0, 0.0, 0.0};
+    par_for(count, g_threads, par_propagate_rows, &c);
+}
+
 void orc_net_gradient_step(orc_net *n, const double *x, const double *t, int32_t B,
                            double step, double momentum, int32_t noise, int32_t faithful) {
+    if (g_threads > 1 && !noise && !faithful && B > 1) {
+        gradient_step_threads(n, x, t, B, step, momentum);
+        return;
+    }
     int d0 = n->dims[0], dl = n->dims[n->n_dims - 1];
     int64_t P = n->n_weights;
     double *agg = NULL;

@@ -101,6 +101,14 @@ void orc_net_gradient_step(orc_net *n, const double *x, const double *t,
                            int32_t B, double step, double momentum,
                            int32_t noise, int32_t faithful);
 
+/* Worker threads for the checker (NOT part of the reference, which is serial): per-sample gradients / per-row forward
+ * passes run on up to `t` threads and are combined in the serial order, so results are bit-identical to t = 1.  The
+ * timed CPU baseline keeps t = 1. */
+void orc_set_threads(int32_t t);
+int32_t orc_get_threads(void);
+void orc_net_loss_rows(orc_net *n, const double *x, const double *t, int64_t count, double *out);
+void orc_net_propagate_rows(orc_net *n, const double *x, int64_t count, double *y);
+
 /* ---- trainer ------------------------------------------------------------ */
 typedef struct orc_sampler orc_sampler;
 /* NeuralNetTrainer.java:28-43,143-168 with IDX order as master order */

@@ -81,8 +81,11 @@ void orc_train(orc_net *n, const double *x, const double *t, int32_t n_rows,
 double orc_validate(orc_net *n, const double *x, const double *t, int32_t count) {
     int d0 = orc_net_input_dim(n), dl = orc_net_output_dim(n);
     double loss = 0;
-    for (int32_t i = 0; i < count; i++)
-        loss += orc_net_loss(n, x + (int64_t)i * d0, t + (int64_t)i * dl);    /* T:110 */
+    (void)d0; (void)dl;
+    double *rows = (double *)malloc(sizeof(double) * (size_t)count);
+    orc_net_loss_rows(n, x, t, count, rows);                                   /* T:110 (threads: rows are independent) */
+    for (int32_t i = 0; i < count; i++) loss += rows[i];                       /* summed in key order like T:108-111 */
+    free(rows);
     return loss / count;                                                       /* T:112 */
 }
 
@@ -90,17 +93,19 @@ double orc_validate(orc_net *n, const double *x, const double *t, int32_t count)
 int64_t orc_evaluate(orc_net *n, const double *x, const int32_t *labels,
                      int64_t n_rows, int32_t *pred_or_null) {
     int d0 = orc_net_input_dim(n), dl = orc_net_output_dim(n);
-    double *out = (double *)malloc(sizeof(double) * dl);
+    (void)d0;
+    double *all = (double *)malloc(sizeof(double) * (size_t)dl * (size_t)n_rows);
+    orc_net_propagate_rows(n, x, n_rows, all);                                 /* M:163 (threads: rows are independent) */
     int64_t hits = 0;
     for (int64_t r = 0; r < n_rows; r++) {
-        orc_net_propagate(n, x + r * d0, out);                                 /* M:163 */
+        const double *out = all + r * dl;
         int actual = 0;
         for (int i = 0; i < dl; i++)
             if (out[i] >= out[actual]) actual = i;                             /* M:166-168 (Q10) */
         if (pred_or_null) pred_or_null[r] = actual;
         if (actual == labels[r]) hits++;                                       /* M:169 */
     }
-    free(out);
+    free(all);
     return hits;
 }
 

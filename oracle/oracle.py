@@ -79,6 +79,8 @@ def lib():
     L.orc_net_weight_gradient.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.orc_net_gradient_step.argtypes = [C.c_void_p, _dp, _dp, C.c_int32, C.c_double, C.c_double,
                                         C.c_int32, C.c_int32]
+    L.orc_set_threads.argtypes = [C.c_int32]
+    L.orc_get_threads.restype = C.c_int32
     L.orc_sampler_create.argtypes = [C.c_int32, C.c_int64]
     L.orc_sampler_create.restype = C.c_void_p
     L.orc_sampler_destroy.argtypes = [C.c_void_p]
@@ -224,6 +226,15 @@ class OracleNet:
         pred = np.empty(x.shape[0], dtype=np.int32)
         hits = lib().orc_evaluate(self._h, _d(x), _i(labels), x.shape[0], _i(pred))
         return hits, pred
+
+
+def set_threads(t):
+    """worker threads of the checker (bit-identical results; the reference and the timed CPU baseline are serial)"""
+    lib().orc_set_threads(int(t))
+
+
+def get_threads():
+    return lib().orc_get_threads()
 
 
 class Sampler:

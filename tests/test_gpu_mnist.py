@@ -55,3 +55,54 @@ def test_mnist_trainer_matches_oracle(g, orc, data_dir, tmp_path, dims, B, step)
     assert test_acc > 0.5                                            # it actually learned the surrogate
     row = open(tmp_path / "logs" / "trainLog.csv").read()
     assert row == orc.format_log_row(dims, iters, step, B, 0.9, False, rh_tr / len(ltr), rh_te / len(lte))
+
+
+@pytest.fixture(scope="module")
+def full_data_dir(tmp_path_factory, golden_dir):
+    """all 60 000 + 10 000 rows: the reference's real label files with the surrogate images"""
+    from gnn_b200 import mnist
+    d = tmp_path_factory.mktemp("mnist_full")
+    mnist.ensure_surrogate(str(d), os.path.join(golden_dir, "mnist"))
+    return str(d)
+
+
+def test_c2_one_full_epoch_matches_oracle(g, orc, full_data_dir, tmp_path):
+    """BASELINE configs[1] across an epoch boundary: 60000 / 16 = 3750 gradient steps of 784-300-100-10 with the literals
+    of MNISTTrainer.main (M:224-230) -- the sampler refills once the epoch is used up (T:147-150) -- plus ten steps of the
+    second epoch, GPU (K1) against the oracle on the same rows in the same order.  Weights within 1e-9 relative, the
+    epoch-boundary loss validate(601) (T:65, T:102-113) within 1e-9, argmax identical on all 10 000 test rows and on
+    the 60 000 training rows, the trainLog.csv row byte-identical.  The oracle runs its per-sample gradients on all
+    host threads (bit-identical to its serial loops, tests/test_oracle.py).  SURROGATE images, not MNIST."""
+    from gnn_b200 import mnist
+    dims, B, step, iters = [784, 300, 100, 10], 16, 0.0125, 3750 + 10
+    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME)
+    tr = g.MNISTTrainer(net, full_data_dir, str(tmp_path / "logs"))
+    assert tr.n_train == 60000 and tr.n_test == 10000
+    tr.train(iters, step, B, 0.9, False, False, False)
+    loss_gpu = tr.trainer.validate(601)
+    train_acc, test_acc = tr.testOnTrainingData(), tr.testOnTestData()
+    tr.logTest(dims, iters, step, B, 0.9, False, train_acc, test_acc)
+
+    xtr = orc.read_idx_images(os.path.join(full_data_dir, "train-images-idx3-ubyte"))
+    ltr = orc.read_idx_labels(os.path.join(full_data_dir, "train-labels-idx1-ubyte"))
+    xte = orc.read_idx_images(os.path.join(full_data_dir, "t10k-images-idx3-ubyte"))
+    lte = orc.read_idx_labels(os.path.join(full_data_dir, "t10k-labels-idx1-ubyte"))
+    ttr = mnist.one_hot(ltr)
+    orc.set_threads(os.cpu_count() or 1)
+    try:
+        ref = orc.OracleNet(dims)
+        ref.train(xtr, ttr, iters, B, step, 0.9)
+        loss_ref = ref.validate(xtr, ttr, 601)
+        rh_tr, rp_tr = ref.evaluate(xtr, ltr)
+        rh_te, rp_te = ref.evaluate(xte, lte)
+    finally:
+        orc.set_threads(1)
+    wr = ref.get_weights()
+    assert np.max(np.abs(net.getWeights() - wr) / np.maximum(1e-3, np.abs(wr))) <= 1e-9
+    assert abs(loss_gpu - loss_ref) <= 1e-9 * max(1.0, abs(loss_ref)), (loss_gpu, loss_ref)
+    _, _, p_te = tr.testingPartition.evaluate(want_pred=True)
+    _, _, p_tr = tr.trainer.dataMaster.evaluate(want_pred=True)
+    assert (p_te == rp_te).all() and (p_tr == rp_tr).all()
+    assert train_acc == rh_tr / 60000 and test_acc == rh_te / 10000
+    row = open(tmp_path / "logs" / "trainLog.csv").read()
+    assert row == orc.format_log_row(dims, iters, step, B, 0.9, False, rh_tr / 60000, rh_te / 10000)

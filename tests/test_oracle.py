@@ -220,3 +220,27 @@ def test_train_matches_manual_loop(orc):
         b.gradient_step(x[i], t[i], 0.05, 0.9)
     assert (a.get_weights() == b.get_weights()).all()
     assert abs(a.validate(x, t, 7) - np.mean([a.loss(x[i], t[i]) for i in range(7)])) < 1e-15
+
+
+def test_worker_threads_are_bit_identical(orc):
+    """orc.set_threads(T): per-sample gradients on T threads, summed in batch order -- the same bits as the serial
+    loops (gradientStep S:305-342, validate T:102-113, the accuracy pass M:159-172) for both net classes"""
+    rng = np.random.RandomState(5)
+    for kind_kw, dims, B in (({}, [30, 17, 11, 6], 8),
+                             (dict(kind=orc.NET_GENERAL, inner_act="sigmoid", inner_param=0.0, last_act="sigmoid"),
+                              [30, 12, 9, 5], 16)):
+        n_rows = 96
+        x = rng.rand(n_rows, dims[0])
+        lab = rng.randint(0, dims[-1], n_rows).astype(np.int32)
+        t = np.zeros((n_rows, dims[-1]))
+        t[np.arange(n_rows), lab] = 1.0
+        out = []
+        for threads in (1, 4):
+            orc.set_threads(threads)
+            net = orc.OracleNet(dims, **kind_kw)
+            losses = net.train(x, t, 12, B, 0.05, 0.9, want_loss=True)
+            out.append((net.get_weights(), net.get_velocity(), losses, net.validate(x, t, 50), net.evaluate(x, lab)))
+        orc.set_threads(1)
+        a, b = out
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+        assert a[3] == b[3] and a[4][0] == b[4][0] and np.array_equal(a[4][1], b[4][1])
