@@ -19,6 +19,10 @@
 //   f64      V[n_weights]
 //   u64      FNV-1a 64 of every byte before it
 // Everything here is host code over b2nn_get_* / b2nn_set_*; only save and load need the GPU.
+#include <fcntl.h>
+#include <unistd.h>
+
+#include <atomic>
 #include <cerrno>
 #include <cstring>
 #include <memory>
@@ -86,7 +90,11 @@ int read_header(FILE *f, Fnv &h, Header &hd, const char *path) {
     int64_t tot = 0;
     for (uint32_t l = 0; l < hd.n_dims; l++) {
         B2_REQUIRE(hd.dims[l] > 0, B2NN_ERR_INVALID_ARG, "%s: layerDims[%u] = %d", path, l, hd.dims[l]);
-        if (l + 1 < hd.n_dims) tot += (int64_t)hd.dims[l] * hd.dims[l + 1];
+        if (l + 1 < hd.n_dims) {
+            // untrusted file: dims are positive int32, so a product fits int64; bound the running sum (2^40 weights = 8 TiB)
+            tot += (int64_t)hd.dims[l] * hd.dims[l + 1];
+            B2_REQUIRE(tot <= ((int64_t)1 << 40), B2NN_ERR_INVALID_ARG, "%s: implausible weight count", path);
+        }
     }
     B2_REQUIRE(tot == hd.n_weights && hd.time >= 0, B2NN_ERR_INVALID_ARG,
                "%s: weight count %lld does not match the layer dimensions (%lld)", path, (long long)hd.n_weights,
@@ -110,8 +118,13 @@ int b2nn_checkpoint_save(b2nn_net *net, const char *path) {
     std::vector<double> w(n), v(n);
     B2_TRY(b2nn_get_weights(net, w.data()));   // synchronises the net's streams
     B2_TRY(b2nn_get_velocity(net, v.data()));
-    // write beside the target and rename: a crash never leaves a half-written checkpoint under `path`
-    const std::string tmp = std::string(path) + ".tmp";
+    // Write beside the target under a name unique to this process and call (two savers of one path -- e.g. several
+    // data-parallel ranks, though only ONE rank should save: they hold identical state -- never share a temp file),
+    // fsync the file, rename it over the target and fsync the directory: a crash or power loss leaves either the old
+    // checkpoint or the complete new one under `path`.
+    static std::atomic<unsigned> counter{0};
+    const std::string tmp = std::string(path) + ".tmp." + std::to_string((long long)getpid()) + "." +
+                            std::to_string(counter.fetch_add(1));
     File f(fopen(tmp.c_str(), "wb"));
     B2_REQUIRE(f != nullptr, B2NN_ERR_INVALID_ARG, "cannot open %s for writing: %s", tmp.c_str(), strerror(errno));
     Fnv h;
@@ -125,7 +138,7 @@ int b2nn_checkpoint_save(b2nn_net *net, const char *path) {
               put(f.get(), h, two, sizeof two) && put(f.get(), h, tw, sizeof tw) &&
               put(f.get(), h, w.data(), n * sizeof(double)) && put(f.get(), h, v.data(), n * sizeof(double));
     const uint64_t sum = h.h;
-    ok = ok && fwrite(&sum, 1, 8, f.get()) == 8 && fflush(f.get()) == 0;
+    ok = ok && fwrite(&sum, 1, 8, f.get()) == 8 && fflush(f.get()) == 0 && fsync(fileno(f.get())) == 0;
     FILE *raw = f.release();
     ok = (fclose(raw) == 0) && ok;
     if (!ok) {
@@ -137,6 +150,13 @@ int b2nn_checkpoint_save(b2nn_net *net, const char *path) {
         set_error("cannot rename %s to %s: %s", tmp.c_str(), path, strerror(errno));
         remove(tmp.c_str());
         return B2NN_ERR_INVALID_ARG;
+    }
+    {   // make the rename itself durable
+        const std::string p(path);
+        const size_t slash = p.find_last_of('/');
+        const std::string dir = slash == std::string::npos ? "." : (slash == 0 ? "/" : p.substr(0, slash));
+        const int dfd = open(dir.c_str(), O_RDONLY | O_DIRECTORY);
+        if (dfd >= 0) { fsync(dfd); close(dfd); }
     }
     return B2NN_OK;
 }

@@ -151,7 +151,8 @@ int b2nn_time(const b2nn_net *net, int64_t *time);
 /* Checkpoint file (the reference has no persistence: a trained net is lost at process exit, and the 500 000-
  * iteration run of logs/trainLog.csv:5 cannot be resumed).  Holds exactly what gradientStep mutates (S:327-344):
  * weights, previousUpdate (velocity) and time, as FP64 in the boundary layout, plus the constructor arguments and a
- * checksum; byte layout in graph-neural-net_b200/csrc/checkpoint.cu.  save writes path + ".tmp" and renames.
+ * checksum; byte layout in graph-neural-net_b200/csrc/checkpoint.cu.  save writes a uniquely named temp file beside
+ * path, fsyncs it, renames it over path and fsyncs the directory (data-parallel groups: ONE rank saves).
  * load requires equal layerDims, net class and activation / loss functions (B2NN_ERR_DIM_MISMATCH otherwise; the
  * precision may differ, so an FP64 run can be resumed in BF16 or TF32 and back) and leaves the net untouched when
  * the file is damaged.  info reads the header only and needs no GPU; any out pointer may be NULL. */
