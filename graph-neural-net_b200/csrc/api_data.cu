@@ -158,7 +158,7 @@ int b2nn_dataset_create(b2nn_net *net, const void *x, int32_t x_dtype, const dou
     if (net->precision == B2NN_PREC_F64)
         B2_REQUIRE(x_dtype == B2NN_DT_F64, B2NN_ERR_UNSUPPORTED, "FP64 nets stage FP64 rows");
     b2nn_dataset *ds = new b2nn_dataset();
-    ds->net = net; ds->n = n; ds->d0 = d0; ds->dL = dL; ds->location = location; ds->x_dtype = x_dtype;
+    ds->net = net; ds->device = net->device; ds->n = n; ds->d0 = d0; ds->dL = dL; ds->location = location; ds->x_dtype = x_dtype;
     const size_t xbytes = (size_t)n * d0 * dtype_size(x_dtype);
     cudaError_t e;
     if (location == B2NN_DATA_DEVICE) {
@@ -223,7 +223,9 @@ int b2nn_dataset_create(b2nn_net *net, const void *x, int32_t x_dtype, const dou
 
 int b2nn_dataset_destroy(b2nn_dataset *ds) {
     if (!ds) return B2NN_OK;
-    if (ds->net) { cudaSetDevice(ds->net->device); cudaDeviceSynchronize(); }
+    // the owning net may already have been destroyed (garbage collectors do not order finalisers): use the recorded device
+    if (cudaSetDevice(ds->device) == cudaSuccess) cudaDeviceSynchronize();
+    else cudaGetLastError();
     if (ds->x) { if (ds->location == B2NN_DATA_DEVICE) cudaFree(ds->x); else cudaFreeHost(ds->x); }
     if (ds->xu8) cudaFree(ds->xu8);
     if (ds->t) cudaFree(ds->t);

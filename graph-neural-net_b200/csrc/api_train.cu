@@ -26,6 +26,17 @@ int ensure_dscratch(b2nn_net *net, size_t bytes) {
     return B2NN_OK;
 }
 
+int ensure_pinned(b2nn_net *net, size_t bytes) {
+    if (bytes <= net->pinned_bytes) return B2NN_OK;
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    if (net->pinned) cudaFreeHost(net->pinned);
+    net->pinned = nullptr;
+    net->pinned_bytes = 0;
+    B2_CHECK_CUDA(cudaHostAlloc(&net->pinned, bytes, cudaHostAllocDefault));
+    net->pinned_bytes = bytes;
+    return B2NN_OK;
+}
+
 int check_net(b2nn_net *net) {
     B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
     B2_CHECK_CUDA(cudaSetDevice(net->device));
@@ -177,9 +188,14 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
         if (f64_fused_supported(net, B)) {
             // the reference's per-step call (T:70, T:89) on the nets K1 serves: the batch is staged as a B-row data set
             // and K1 runs ONE step over rows 0..B-1 -- one launch instead of a dozen, same arithmetic as the fast path
+            // (the caller's arrays are pageable: staged through a pinned buffer so that the two copies are plain DMAs)
             const int d0 = net->dims[0];
-            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.xin, x, (size_t)B * d0 * sizeof(double), cudaMemcpyHostToDevice, net->stream));
-            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.t, t, (size_t)B * dL * sizeof(double), cudaMemcpyHostToDevice, net->stream));
+            const size_t xb = (size_t)B * d0 * sizeof(double), tb = (size_t)B * dL * sizeof(double);
+            B2_TRY(ensure_pinned(net, xb + tb));
+            memcpy(net->pinned, x, xb);
+            memcpy((char *)net->pinned + xb, t, tb);
+            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.xin, net->pinned, xb, cudaMemcpyHostToDevice, net->stream));
+            B2_CHECK_CUDA(cudaMemcpyAsync(net->fw.t, (char *)net->pinned + xb, tb, cudaMemcpyHostToDevice, net->stream));
             B2_TRY(f64_iota(net, B));
             double *loss_dev = mean_loss_or_null ? (double *)net->dscratch : nullptr;
             B2_TRY(f64_fused_train(net, net->fw.xin, nullptr, net->fw.t, nullptr, net->fw.idx, 1, B, step, momentum, loss_dev));

@@ -115,7 +115,8 @@ struct WideBatch {
 }  // namespace b2nn
 
 struct b2nn_dataset {
-    b2nn_net *net = nullptr;
+    b2nn_net *net = nullptr;  // identity check only (check_pair): never dereferenced at destroy time, the net may be gone
+    int device = 0;           // device the rows were staged on
     int64_t n = 0;
     int d0 = 0, dL = 0;
     int location = 0;
@@ -154,6 +155,7 @@ struct b2nn_net {
         double *row_loss = nullptr;     // [rows]
         int32_t *pred = nullptr;        // [rows]
         int32_t *idx = nullptr;
+        int iota_rows = 0;              // idx[0..iota_rows) currently holds 0, 1, 2, .. (f64_iota)
         double *xin = nullptr;          // staged input rows
     } fw;
     double *f64_grad = nullptr;  // [P] scratch for weight_gradient
@@ -161,6 +163,7 @@ struct b2nn_net {
     struct Fused {
         double *V0t = nullptr, *V1b = nullptr, *V2r = nullptr, *z1buf = nullptr, *z2buf = nullptr;
         unsigned long long *bar = nullptr;
+        unsigned long long bar_base = 0;     // arrivals counted in bar[0] by the launches so far
         unsigned long long *prof = nullptr;  // [16] phase cycle sums of CTA 0 (b2nn_k1_profile / B2NN_K1_PROF)
         int cap_B = 0;
     } fused;

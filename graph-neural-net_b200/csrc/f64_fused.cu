@@ -107,7 +107,10 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     // cp.async.bulk needs 16-byte aligned rows (global source, shared destination) and sizes
     p.bulk = Xu8 ? (d0 % 16 == 0) : (d0 % 2 == 0);
     if (getenv("B2NN_F64_NO_BULK")) p.bulk = 0;
-    B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, sizeof(unsigned long long), net->stream));
+    // the barrier counter only ever grows: this launch starts from where the previous ones left it (2 barriers of G
+    // arrivals per step), so no reset is needed between launches
+    p.bar_base = fs.bar_base;
+    fs.bar_base += 2ull * (unsigned long long)G * (unsigned long long)iters;
     unsigned long long *&prof_dev = fs.prof;   // per net (hence per device)
     const bool prof = getenv("B2NN_K1_PROF") != nullptr || net->k1_prof;
     if (prof) {

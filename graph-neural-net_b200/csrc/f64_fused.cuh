@@ -37,7 +37,8 @@ struct FusedParams {
     double *V2r;            // [grid][d2*d3] scratch: per-CTA velocity replica of W2
     double *z1buf;          // [2][B][d1] published pre-activations (double buffered by step parity)
     double *z2buf;          // [2][B][d2]
-    unsigned long long *bar;  // [2]: grid barrier counter (zeroed before launch); sticky give-up word
+    unsigned long long *bar;  // [2]: grid barrier counter (never reset: bar_base = its value when this launch starts); sticky give-up word
+    unsigned long long bar_base;
     double *loss_out;       // [iters] sum over the batch of per-sample losses, or null
     // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
     int nc0max, nc1max;
@@ -269,7 +270,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     __syncthreads();
     if (p.bulk && warp == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar, lane);
 
-    unsigned long long bar_target = 0;
+    unsigned long long bar_target = p.bar_base;
     bool gave_up = false;  // thread 0: a grid-barrier wait ran out of polls (see grid_barrier_wait)
     unsigned long long *profs = reinterpret_cast<unsigned long long *>(sm + p.o_prof);
     if (p.prof != nullptr && c == 0 && tid == 0)

@@ -73,6 +73,7 @@ int f64_ensure_work(b2nn_net *net, int rows) {
     const int nd = net->n_dims;
     fw.z.assign(nd, nullptr); fw.a.assign(nd, nullptr); fw.d.assign(nd, nullptr);
     fw.cap_rows = 0;
+    fw.iota_rows = 0;
     for (int l = 0; l < nd; l++) {
         const size_t n = (size_t)rows * net->dims[l] * sizeof(double);
         B2_CHECK_CUDA(cudaMalloc(&fw.z[l], n));
@@ -170,6 +171,8 @@ int f64_gradients(b2nn_net *net, int rows, double step, double momentum, double 
 }
 
 int f64_iota(b2nn_net *net, int rows) {
+    if (net->fw.iota_rows >= rows) return B2NN_OK;
+    net->fw.iota_rows = rows;
     f64::iota_rows<<<(rows + 127) / 128, 128, 0, net->stream>>>(net->fw.idx, rows);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
