@@ -315,7 +315,12 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             const int32_t r = idx[B + b];
             tnext = p.T ? p.T[(size_t)r * d3 + j] : ((p.labels[r] == j) ? 1.0 : 0.0);
         }
-        if (p.bulk) {
+        // pixel-byte rows of step it >= 1 were already converted into a0 by the upper half of the CTA during phase 5 of
+        // step it - 1 (see there); only step 0 converts here
+        const bool staged_early = p.bulk && u8 && it > 0;
+        if (staged_early) {
+            K1_MARK(15)
+        } else if (p.bulk) {
             mbar_wait_parity(mbar, (uint32_t)(it & 1));
             K1_MARK(15)  // targets + wait for the prefetched rows
             if (u8) {
@@ -565,9 +570,29 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             __syncthreads();
             if (warp == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar, lane);
         }
+        // Pixel-byte rows: the next batch has been sitting in `stage` since barrier 1 and a0 is free from here on, so the
+        // upper half of the warps turns it into a0 = f(byte / 255) now, while the lower half applies the W1 / W2 updates
+        // (latency-bound loops: half the threads take little longer) -- the next step starts with its batch staged.
+        const bool conv_next = p.bulk && u8 && have_next;
+        int ut = tid, un = NT;   // thread index / count of the update loops below
+        if (conv_next) {
+            __syncthreads();     // every thread is done reading a0 (W0 gradient)
+            un = NT / 2;
+            if (tid >= un) {
+                mbar_wait_parity(mbar, (uint32_t)((it + 1) & 1));
+                const uint32_t *st4 = reinterpret_cast<const uint32_t *>(stage);
+                double2 *a02 = reinterpret_cast<double2 *>(a0);
+                for (int q = tid - un; q < B * d0 / 4; q += un) {
+                    const uint32_t v = st4[q];
+                    a02[2 * q] = make_double2(lut[v & 0xff], lut[(v >> 8) & 0xff]);
+                    a02[2 * q + 1] = make_double2(lut[(v >> 16) & 0xff], lut[v >> 24]);
+                }
+                ut = NT;         // ... and takes no part in the update loops
+            }
+        }
         // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
         for (int kk = 0; kk < nc1; kk++)
-            for (int j = tid; j < d1; j += NT) {
+            for (int j = ut; j < d1; j += un) {
                 double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
                 const double vprev = *vp;
                 double g = 0.0;
@@ -578,7 +603,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         K1_MARK(13)
         // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
-        for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
+        for (int e = ut; e < nc0 * d2; e += un) {  // all (row, column) pairs at once: one L2 round trip, not nc0
             const int jj = e / d2, k = e - jj * d2;
             double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
             const double vprev = *vp;
@@ -590,7 +615,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(14)
         // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
-        for (int e = tid; e < d2 * d3; e += NT) {
+        for (int e = ut; e < d2 * d3; e += un) {
             const int i = e / d3, j = e - i * d3;
             const double vprev = v2[e];
             double g = 0.0;
