@@ -163,8 +163,7 @@ struct b2nn_net {
     struct Fused {
         double *V0t = nullptr, *V1b = nullptr, *V2r = nullptr, *z1buf = nullptr, *z2buf = nullptr;
         unsigned long long *bar = nullptr;
-        unsigned long long bar_base = 0;     // arrivals counted (over all shards) by the launches so far
-        int bar_shards = 16;                 // arrival counters of the grid barrier (f64_fused.cuh)
+        unsigned long long bar_base = 0;     // arrivals counted in bar[0] by the launches so far
         unsigned long long *prof = nullptr;  // [16] phase cycle sums of CTA 0 (b2nn_k1_profile / B2NN_K1_PROF)
         int cap_B = 0;
     } fused;

@@ -90,13 +90,8 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
         B2_CHECK_CUDA(cudaMalloc(&fs.V0t, (size_t)d1 * d0 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.V1b, (size_t)d1 * d2 * sizeof(double)));
         B2_CHECK_CUDA(cudaMalloc(&fs.V2r, (size_t)G * d2 * d3 * sizeof(double)));
-        B2_CHECK_CUDA(cudaMalloc(&fs.bar, f64::K1_BAR_WORDS * sizeof(unsigned long long)));
-        B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, f64::K1_BAR_WORDS * sizeof(unsigned long long), net->stream));
-        fs.bar_shards = 16;
-        if (const char *e = getenv("B2NN_K1_SHARDS")) {   // measurement knob: 1 = the single counter of round 1
-            const int v = atoi(e);
-            if (v >= 1 && v <= f64::K1_MAX_SHARDS) fs.bar_shards = v;
-        }
+        B2_CHECK_CUDA(cudaMalloc(&fs.bar, 2 * sizeof(unsigned long long)));
+        B2_CHECK_CUDA(cudaMemsetAsync(fs.bar, 0, 2 * sizeof(unsigned long long), net->stream));
         B2_CHECK_CUDA(cudaFuncSetAttribute(fused_kernel_for(net->inner_act),
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, net->max_smem_optin));
     }
@@ -115,7 +110,6 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     // the barrier counter only ever grows: this launch starts from where the previous ones left it (2 barriers of G
     // arrivals per step), so no reset is needed between launches
     p.bar_base = fs.bar_base;
-    p.bar_shards = fs.bar_shards;
     fs.bar_base += 2ull * (unsigned long long)G * (unsigned long long)iters;
     unsigned long long *&prof_dev = fs.prof;   // per net (hence per device)
     const bool prof = getenv("B2NN_K1_PROF") != nullptr || net->k1_prof;
@@ -146,8 +140,6 @@ int f64_fused_train(b2nn_net *net, const double *X, const uint8_t *Xu8, const do
     }
     return B2NN_OK;
 }
-
-int f64_giveup_word() { return f64::K1_GIVEUP_WORD; }
 
 void f64_fused_free(b2nn_net *net) {
     auto &fs = net->fused;

@@ -37,9 +37,8 @@ struct FusedParams {
     double *V2r;            // [grid][d2*d3] scratch: per-CTA velocity replica of W2
     double *z1buf;          // [2][B][d1] published pre-activations (double buffered by step parity)
     double *z2buf;          // [2][B][d2]
-    unsigned long long *bar;  // [K1_BAR_WORDS]: sharded grid-barrier counters (never reset: bar_base = their sum when this launch starts) + sticky give-up word
+    unsigned long long *bar;  // [2]: grid barrier counter (never reset: bar_base = its value when this launch starts); sticky give-up word
     unsigned long long bar_base;
-    int bar_shards;              // arrival counters in use (<= K1_MAX_SHARDS)
     double *loss_out;       // [iters] sum over the batch of per-sample losses, or null
     // shared-memory carve-up (in doubles), computed by the host with the same slice formulas
     int nc0max, nc1max;
@@ -58,61 +57,45 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
-// Grid barrier over a SHARDED arrival counter.  148 CTAs arriving on one address serialise in the L2 atomic unit
-// (~27 cycles per same-address atomic: ~4 K cycles per barrier, the bulk of the 5-7 K the single counter cost), so
-// CTA c arrives on shard c % S (each shard in its own 128-byte line) and warp 0 waits by polling all S shards at once
-// -- one lane per shard, one L2 round trip per poll like before -- until their sum reaches `target`.  The counters only
-// grow (FusedParams::bar_base carries the sum from launch to launch).
-// Bounded: a cooperative launch keeps every CTA resident, so the only way to wait forever is a CTA that died; after
-// K1_MAX_POLLS polls (each an L2 round trip: seconds in total) the CTA records the fact in the give-up word (the host turns
-// it into B2NN_ERR_CUDA), stops waiting for good and lets the launch end.
+// Wait (thread 0) until the barrier counter reaches `target`.  Bounded: a cooperative launch keeps every CTA resident, so
+// the only way to wait forever is a CTA that died; after K1_MAX_POLLS polls (each an L2 round trip: seconds in total)
+// the CTA records the fact in bar[1] (the host turns it into B2NN_ERR_CUDA), stops waiting for good and lets the launch end.
 constexpr unsigned int K1_MAX_POLLS = 1u << 24;
-constexpr int K1_MAX_SHARDS = 32;
-constexpr int K1_SHARD_STRIDE = 16;                                   // unsigned long longs per shard: one 128-byte line
-constexpr int K1_GIVEUP_WORD = K1_MAX_SHARDS * K1_SHARD_STRIDE;       // index of the sticky give-up word
-constexpr int K1_BAR_WORDS = K1_GIVEUP_WORD + K1_SHARD_STRIDE;
-
-__device__ __forceinline__ void grid_barrier_arrive(unsigned long long *bar, int shards) {
-    __threadfence();
-    atomicAdd(bar + (size_t)(blockIdx.x % shards) * K1_SHARD_STRIDE, 1ULL);
-}
-// called by ALL lanes of warp 0
-__device__ __forceinline__ void grid_barrier_wait(unsigned long long *bar, int shards, unsigned long long target,
-                                                  bool &gave_up) {
+__device__ __forceinline__ void grid_barrier_wait(unsigned long long *bar, unsigned long long target, bool &gave_up) {
     if (gave_up) return;
-    const int lane = threadIdx.x & 31;
-    unsigned long long sum;
+    unsigned long long v;
     unsigned int polls = 0;
     do {
-        unsigned long long v = 0;
-        if (lane < shards)
-            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar + (size_t)lane * K1_SHARD_STRIDE) : "memory");
-        sum = v;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    } while (sum < target && ++polls < K1_MAX_POLLS);
-    if (sum < target) {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+    } while (v < target && ++polls < K1_MAX_POLLS);
+    if (v < target) {
         gave_up = true;
-        if (lane == 0) atomicMax(bar + K1_GIVEUP_WORD, (unsigned long long)polls);
+        atomicMax(bar + 1, (unsigned long long)polls);
     }
 }
 
-__device__ __forceinline__ void grid_barrier(unsigned long long *bar, int shards, unsigned long long target, bool &gave_up) {
+__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target, bool &gave_up) {
     __syncthreads();
-    if (threadIdx.x == 0) grid_barrier_arrive(bar, shards);
-    if (threadIdx.x < 32) grid_barrier_wait(bar, shards, target, gave_up);
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1ULL);
+        grid_barrier_wait(bar, target, gave_up);
+    }
     __syncthreads();
 }
 
-// the same barrier with `work()` run by the whole CTA between this CTA's arrival and the wait for the others: warp 0
+// the same barrier with `work()` run by the whole CTA between this CTA's arrival and the wait for the others: thread 0
 // polls, every other warp is idle there anyway
 template <class F>
-__device__ __forceinline__ void grid_barrier_overlap(unsigned long long *bar, int shards, unsigned long long target,
-                                                     bool &gave_up, F work) {
+__device__ __forceinline__ void grid_barrier_overlap(unsigned long long *bar, unsigned long long target, bool &gave_up,
+                                                     F work) {
     __syncthreads();
-    if (threadIdx.x == 0) grid_barrier_arrive(bar, shards);
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1ULL);
+    }
     work();
-    if (threadIdx.x < 32) grid_barrier_wait(bar, shards, target, gave_up);
+    if (threadIdx.x == 0) grid_barrier_wait(bar, target, gave_up);
     __syncthreads();
 }
 
@@ -288,7 +271,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     if (p.bulk && warp == 0) issue_batch_fetch(p, 0, u8 ? (void *)stage : (void *)a0, mbar, lane);
 
     unsigned long long bar_target = p.bar_base;
-    bool gave_up = false;  // warp 0: a grid-barrier wait ran out of polls (see grid_barrier_wait)
+    bool gave_up = false;  // thread 0: a grid-barrier wait ran out of polls (see grid_barrier_wait)
     unsigned long long *profs = reinterpret_cast<unsigned long long *>(sm + p.o_prof);
     if (p.prof != nullptr && c == 0 && tid == 0)
         for (int i = 0; i < 16; i++) profs[i] = 0ULL;
@@ -315,12 +298,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             const int32_t r = idx[B + b];
             tnext = p.T ? p.T[(size_t)r * d3 + j] : ((p.labels[r] == j) ? 1.0 : 0.0);
         }
-        // pixel-byte rows of step it >= 1 were already converted into a0 by the upper half of the CTA during phase 5 of
-        // step it - 1 (see there); only step 0 converts here
-        const bool staged_early = p.bulk && u8 && it > 0;
-        if (staged_early) {
-            K1_MARK(15)
-        } else if (p.bulk) {
+        if (p.bulk) {
             mbar_wait_parity(mbar, (uint32_t)(it & 1));
             K1_MARK(15)  // targets + wait for the prefetched rows
             if (u8) {
@@ -369,7 +347,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         bar_target += G;
         // the byte staging buffer has been free since the batch was staged: warp 1 requests the NEXT batch while
         // thread 0 waits for the other CTAs
-        grid_barrier_overlap(p.bar, p.bar_shards, bar_target, gave_up, [&] {
+        grid_barrier_overlap(p.bar, bar_target, gave_up, [&] {
             if (p.bulk && u8 && warp == 1 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar, lane);
         });
         K1_MARK(2)  // barrier 1
@@ -402,7 +380,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(3)  // phase 2
         bar_target += G;
-        grid_barrier(p.bar, p.bar_shards, bar_target, gave_up);
+        grid_barrier(p.bar, bar_target, gave_up);
         K1_MARK(4)  // barrier 2
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
@@ -570,29 +548,9 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             __syncthreads();
             if (warp == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar, lane);
         }
-        // Pixel-byte rows: the next batch has been sitting in `stage` since barrier 1 and a0 is free from here on, so the
-        // upper half of the warps turns it into a0 = f(byte / 255) now, while the lower half applies the W1 / W2 updates
-        // (latency-bound loops: half the threads take little longer) -- the next step starts with its batch staged.
-        const bool conv_next = p.bulk && u8 && have_next;
-        int ut = tid, un = NT;   // thread index / count of the update loops below
-        if (conv_next) {
-            __syncthreads();     // every thread is done reading a0 (W0 gradient)
-            un = NT / 2;
-            if (tid >= un) {
-                mbar_wait_parity(mbar, (uint32_t)((it + 1) & 1));
-                const uint32_t *st4 = reinterpret_cast<const uint32_t *>(stage);
-                double2 *a02 = reinterpret_cast<double2 *>(a0);
-                for (int q = tid - un; q < B * d0 / 4; q += un) {
-                    const uint32_t v = st4[q];
-                    a02[2 * q] = make_double2(lut[v & 0xff], lut[(v >> 8) & 0xff]);
-                    a02[2 * q + 1] = make_double2(lut[(v >> 16) & 0xff], lut[v >> 24]);
-                }
-                ut = NT;         // ... and takes no part in the update loops
-            }
-        }
         // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
         for (int kk = 0; kk < nc1; kk++)
-            for (int j = ut; j < d1; j += un) {
+            for (int j = tid; j < d1; j += NT) {
                 double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
                 const double vprev = *vp;
                 double g = 0.0;
@@ -603,7 +561,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             }
         K1_MARK(13)
         // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
-        for (int e = ut; e < nc0 * d2; e += un) {  // all (row, column) pairs at once: one L2 round trip, not nc0
+        for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
             const int jj = e / d2, k = e - jj * d2;
             double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
             const double vprev = *vp;
@@ -615,7 +573,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(14)
         // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
-        for (int e = ut; e < d2 * d3; e += un) {
+        for (int e = tid; e < d2 * d3; e += NT) {
             const int i = e / d3, j = e - i * d3;
             const double vprev = v2[e];
             double g = 0.0;

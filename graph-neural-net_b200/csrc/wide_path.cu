@@ -638,7 +638,6 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
     return B2NN_OK;
 }
 
-int f64_giveup_word();  // f64_fused.cu
 // A bounded cross-GPU wait of the exchange kernel (dp_kernels.cuh) or of K1's grid barrier gave up: the word it left
 // behind becomes B2NN_ERR_CUDA here.  Called where the host synchronises anyway (b2nn_sync, calls that return data).
 int check_device_error_words(b2nn_net *net) {
@@ -658,7 +657,7 @@ int check_device_error_words(b2nn_net *net) {
     }
     if (net->fused.bar) {
         unsigned long long e = 0;
-        B2_CHECK_CUDA(cudaMemcpyAsync(&e, net->fused.bar + f64_giveup_word(), sizeof e, cudaMemcpyDeviceToHost, net->stream));
+        B2_CHECK_CUDA(cudaMemcpyAsync(&e, net->fused.bar + 1, sizeof e, cudaMemcpyDeviceToHost, net->stream));
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
         B2_REQUIRE(e == 0, B2NN_ERR_CUDA, "the fused FP64 training kernel gave up waiting at a grid barrier (%llu polls)", e);
     }
