@@ -533,6 +533,20 @@ def measure_f64(ctx, name, K, W, x=None, labels=None, want_cpu=False):
                                          "path": "b2nn_gradient_step (NeuralNet.gradientStep, S:297): host double rows "
                                                  "and targets in, one K1 step, stream sync before return"}}
 
+    # K2: batched FP64 inference with the `>=` argmax and the per-row loss (testOnTrainingData / validate, M:159-197,
+    # T:102-113) over all staged rows, one b2nn_evaluate call
+    ds.evaluate()
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    reps = 3
+    for _ in range(reps):
+        hits, mean_loss, _ = ds.evaluate()
+    ev_s = (time.perf_counter() - t2) / reps
+    res["k2_evaluate"] = {"rows": int(x.shape[0]), "ms_per_call": ev_s * 1e3, "rows_per_s": x.shape[0] / ev_s,
+                          "fp64_gflops": 2.0 * n_weights(dims) * x.shape[0] / ev_s / 1e9,
+                          "kernels": "f64::gather_rows + gemm_strict (ascending-k, un-fused multiply-add, like the JVM) per "
+                                     "layer + output_rows + reduce_rows, chunks of 8192 rows; wall clock incl. the sync"}
+
     # K1 phase counters (cycles per step on CTA 0): the latency chain this kernel is bound by
     net.k1Profile(True)
     kp = min(K, 2000)
