@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb2nn.so")
+# B2NN_LIB selects a measurement variant of the library (build.py --variant); the product is lib/libb2nn.so
+LIB_PATH = os.environ.get("B2NN_LIB") or os.path.join(_HERE, "lib", "libb2nn.so")
 
 OK = 0
 ERR_INVALID_ARG, ERR_DIM_MISMATCH, ERR_UNSUPPORTED, ERR_CUDA, ERR_NCCL, ERR_OOM, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6, -7

@@ -36,6 +36,31 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
+def build_variant(name, defines):
+    """a measurement variant of the library (lib/libb2nn_<name>.so, selected with B2NN_LIB=<path>): the same sources
+    compiled with extra -D flags into their own object directory"""
+    objdir = os.path.join(OBJDIR, name)
+    os.makedirs(objdir, exist_ok=True)
+    lib = os.path.join(LIBDIR, "libb2nn_%s.so" % name)
+    objs = []
+
+    def one(src):
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        cmd = [NVCC] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-c", os.path.join(CSRC, src), "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
+        return obj
+
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(one, SOURCES))
+    r = subprocess.run([NVCC, "-shared", "-o", lib] + objs + ["-ldl", "-gencode", "arch=compute_100a,code=sm_100a"],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
+    return lib
+
+
 def build(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
     os.makedirs(OBJDIR, exist_ok=True)
@@ -65,4 +90,7 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if len(sys.argv) > 2 and sys.argv[1] == "--variant":      # build.py --variant e16 B2NN_GEMM_EPI_WARPS=16
+        print(build_variant(sys.argv[2], sys.argv[3:]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -47,7 +47,13 @@ constexpr int GEMM_BM = 128;        // rows of A per CTA (pair tile: 256)
 constexpr int GEMM_BN = 256;        // pair tile width
 constexpr int GEMM_BK = 64;         // 64 bf16 = 128 B = one swizzle row (BF16 operands; GemmCfg<true> for TF32)
 constexpr int GEMM_STAGES = 6;
-constexpr int GEMM_EPI_WARPS = 8;   // two warps per TMEM lane quarter, each draining half the columns
+#ifndef B2NN_GEMM_EPI_WARPS
+#define B2NN_GEMM_EPI_WARPS 8
+#endif
+constexpr int GEMM_EPI_WARPS = B2NN_GEMM_EPI_WARPS;   // GEMM_EPI_PARTS warps per TMEM lane quarter, each draining 1/PARTS of the columns
+constexpr int GEMM_EPI_PARTS = GEMM_EPI_WARPS / 4;
+static_assert(GEMM_EPI_WARPS % 4 == 0 && (GEMM_EPI_PARTS == 1 || GEMM_EPI_PARTS == 2 || GEMM_EPI_PARTS == 4),
+              "epilogue warps come in groups of four (one per TMEM lane quarter); 128-column half tiles split into <= 4 parts of 32");
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 constexpr int GEMM_CHUNK_BYTES = 64 * GEMM_BK * 2;      // one 64 x 64 TMA box: 8 KB
 constexpr int GEMM_A_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of A
@@ -535,7 +541,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     } else {
         // ===================== epilogue warps: each CTA drains its own 128 rows =====================
         const int q = warp & 3;                 // TMEM lane quarter this warp may access
-        const int part = (warp - 2) >> 2;       // which half of the tile's columns
+        const int part = (warp - 2) >> 2;       // which share of the tile's columns
         int acc = 0;
         uint32_t acc_phase = 0;
         uint32_t st_tfull = 0, st_busy = 0;
@@ -547,7 +553,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
             const uint32_t c1 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::tc_fence_after();
             const int m = m0 + rank * GEMM_BM + q * 32 + lane;
-            const int cbeg = part * (bn / 2), cend = cbeg + bn / 2;
+            const int cbeg = part * (bn / GEMM_EPI_PARTS), cend = cbeg + bn / GEMM_EPI_PARTS;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * GEMM_BN;
 #pragma unroll 1
             for (int c0 = cbeg; c0 < cend; c0 += 32) {
