@@ -241,7 +241,7 @@ int b2nn_gradient_step(b2nn_net *net, const double *x, const double *t, int32_t 
     } else {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     }
-    return B2NN_OK;
+    return net->world > 1 ? check_device_error_words(net) : B2NN_OK;   // a peer that never arrived (bounded waits)
 }
 
 int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, const int32_t *labels, int32_t B,
@@ -267,7 +267,7 @@ int b2nn_gradient_step_labeled(b2nn_net *net, const void *x, int32_t x_dtype, co
     } else {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     }
-    return B2NN_OK;
+    return net->world > 1 ? check_device_error_words(net) : B2NN_OK;   // a peer that never arrived (bounded waits)
 }
 
 }  // extern "C"

@@ -179,3 +179,35 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16"):
                  replicas_equal=int(flag.item()), launches=net.kernelLaunches(), mode=net.commMode())
     dist.barrier()
     dist.destroy_process_group()
+
+
+def timeout_worker(rank, world, port, out_dir):
+    """rank 1 joins the group but never takes the step: rank 0's exchange kernel must give up after B2NN_DP_TIMEOUT_MS
+    and the call must come back with an error instead of hanging"""
+    import time
+    import torch
+    import __graft_entry__ as ge
+    os.environ["B2NN_DP_TIMEOUT_MS"] = "300"
+    os.environ["B2NN_DP"] = "p2p"
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    g = ge.load_package()
+    dims = [256, 128, 40]
+    net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=g.capi.PREC_BF16,
+                                         flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX, device=rank)
+    g.dp.init_comm(net, dist)
+    rng = np.random.RandomState(3)
+    x = rng.rand(64, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], 64).astype(np.int32)
+    outcome = "no error"
+    if rank == 0:
+        t0 = time.time()
+        try:
+            net.gradientStepLabeled(x, lab, 0.05, 0.9)
+            net.sync()
+        except g.capi.B2nnError as e:
+            outcome = "B2nnError %d after %.1f s: %s" % (e.code, time.time() - t0, e)
+        with open(os.path.join(out_dir, "timeout.txt"), "w") as f:
+            f.write(outcome)
+    dist.barrier()      # rank 1 stays alive (its arena mapped) until rank 0 is through
+    dist.destroy_process_group()

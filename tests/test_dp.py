@@ -115,3 +115,47 @@ def test_world_matches_single_gpu(g, tmp_path, mode, world, prec, monkeypatch):
     assert int(r["launches"]) > 0
     assert str(r["mode"]) == mode, (str(r["mode"]), mode)
     print("exchange:", str(r["mode"]), "rel", rel)
+
+
+@pytest.mark.gpu
+def test_exchange_wait_is_bounded(g, tmp_path):
+    """every cross-GPU wait of the fused exchange kernel is bounded (B2NN_DP_TIMEOUT_MS): when a peer never takes the
+    step, the kernel gives up, skips its work, and the call returns B2NN_ERR_CUDA naming the wait -- no hang"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from tests import dp_workers
+    mp.spawn(dp_workers.timeout_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    outcome = open(tmp_path / "timeout.txt").read()
+    assert outcome.startswith("B2nnError -4") and "timed out" in outcome and "peer rank 1" in outcome, outcome
+
+
+@pytest.mark.gpu
+def test_two_nets_on_two_devices_in_one_process(g):
+    """function attributes (the GEMM's 198 KB of dynamic shared memory, the carve-out preference of the side kernels)
+    are per DEVICE: a second net on another GPU of the same process must launch and compute the same bits"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    dims, B = [512, 384, 100], 128
+    rng = np.random.RandomState(2)
+    x = rng.rand(B, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], B).astype(np.int32)
+    out = []
+    for dev in (0, 1):
+        for prec in (g.capi.PREC_BF16, g.capi.PREC_TF32):
+            net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=prec,
+                                                 flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX, device=dev)
+            for _ in range(2):
+                net.gradientStepLabeled(x, lab, 0.05, 0.9)
+            out.append(net.getWeights())
+            net.close()
+        f64 = g.SoftmaxCrossEntropyNeuralNet([784, 100, 50, 10], g.LEAKY_RELU, g.LEAKY_RELU_PRIME, device=dev)
+        xs = rng.rand(8, 784)
+        t = np.zeros((8, 10))
+        t[np.arange(8), rng.randint(0, 10, 8)] = 1.0
+        f64.gradientStep((xs, t), 0.01, 0.9)        # K1 on this device
+        assert np.isfinite(f64.getWeights()).all()
+        f64.close()
+    assert np.array_equal(out[0], out[2]) and np.array_equal(out[1], out[3])
