@@ -190,18 +190,38 @@ static __global__ void iota_rows(int32_t *idx, int rows) {
     if (r < rows) idx[r] = r;
 }
 
-// sequential (row-order) sum of per-row losses and hit count; one thread -- tiny inputs
-static __global__ void reduce_rows(const double *loss, const int32_t *pred, const int32_t *labels, int rows,
-                            double *loss_sum, long long *hits) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// Row-order sum of the per-row losses and the hit count (T:108-111 adds the losses in key order; the order is kept so the
+// sum has the reference's bits).  One block: all threads fetch a slab of 256 losses into shared memory at once (one L2
+// round trip per slab instead of one per row), thread 0 adds the slab in ascending row order; hits are counted by all
+// threads (integer, order-free).
+static __global__ void __launch_bounds__(256) reduce_rows(const double *loss, const int32_t *pred, const int32_t *labels,
+                                                          int rows, double *loss_sum, long long *hits) {
+    __shared__ double slab[256];
+    __shared__ int s_hits[256];
+    const int tid = threadIdx.x;
     double s = 0.0;
-    long long h = 0;
-    for (int r = 0; r < rows; r++) {
-        if (loss) s = __dadd_rn(s, loss[r]);
-        if (pred && labels && pred[r] == labels[r]) h++;
+    int h = 0;
+    for (int base = 0; base < rows; base += 256) {
+        const int r = base + tid;
+        if (loss) slab[tid] = r < rows ? loss[r] : 0.0;
+        if (pred && labels && r < rows && pred[r] == labels[r]) h++;
+        __syncthreads();
+        if (loss && tid == 0) {
+            const int n = min(256, rows - base);
+            for (int i = 0; i < n; i++) s = __dadd_rn(s, slab[i]);
+        }
+        __syncthreads();
     }
-    if (loss_sum) *loss_sum = __dadd_rn(*loss_sum, s);
-    if (hits) *hits += h;
+    s_hits[tid] = h;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (tid < o) s_hits[tid] += s_hits[tid + o];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (loss_sum) *loss_sum = __dadd_rn(*loss_sum, s);
+        if (hits) *hits += s_hits[0];
+    }
 }
 
 }  // namespace f64

@@ -181,7 +181,7 @@ int f64_iota(b2nn_net *net, int rows) {
 
 int f64_reduce(b2nn_net *net, int rows, const int32_t *labels_dev, double *loss_sum_dev, long long *hits_dev) {
     auto &fw = net->fw;
-    f64::reduce_rows<<<1, 32, 0, net->stream>>>(loss_sum_dev ? fw.row_loss : nullptr, hits_dev ? fw.pred : nullptr,
+    f64::reduce_rows<<<1, 256, 0, net->stream>>>(loss_sum_dev ? fw.row_loss : nullptr, hits_dev ? fw.pred : nullptr,
                                                 labels_dev, rows, loss_sum_dev, hits_dev);
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
