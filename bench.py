@@ -319,11 +319,14 @@ def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, wan
     B = wl["batch"] // world if strong else wl["batch"]        # rows per GPU per step
     gB = B * world
     prec_name = "tf32" if tf32 else "bf16"
+    # --wire bf16 (opt-in, B2NN_FLAG_BF16_WIRE): per-GPU gradients exchanged as BF16; dp_check reports what it costs
+    wire_flag = g.capi.FLAG_BF16_WIRE if (os.environ.get("B2NN_BENCH_WIRE") == "bf16" and not tf32) else 0
 
     def make_net():
         return g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME,
                                               precision=g.capi.PREC_TF32 if tf32 else g.capi.PREC_BF16,
-                                              flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX, device=dev)
+                                              flags=g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX | wire_flag,
+                                              device=dev)
 
     net = make_net()
     if world > 1:
@@ -340,7 +343,7 @@ def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, wan
     net.setStream(ctx.stream.cuda_stream)
     res = {"workload": name + ": " + (wl["desc"].replace("BF16", "TF32") if tf32 else wl["desc"]), "dims": dims,
            "dtype": prec_name, "batch_per_gpu": B, "global_batch": gB, "scaling": wl["scaling"],
-           "exchange": net.commMode()}
+           "exchange": net.commMode(), "gradient_wire": "bf16" if (wire_flag and world > 1) else "fp32"}
 
     if world > 1 and want_dp_check:
         res["dp_check"] = dp_check(ctx, net, make_net, dims, B, step)
@@ -647,7 +650,8 @@ def run_b2nn(args):
             "vs_baseline": None, "dtype": main["dtype"], "data": "synthetic",
             "config": {"workload": main["workload"], "dims": dims, "batch_per_gpu": main["batch_per_gpu"],
                        "global_batch": main["global_batch"], "parallelism": par,
-                       "exchange": main.get("exchange", "single"), "replicas": world if not wide else None, "l2": l2},
+                       "exchange": main.get("exchange", "single"), "gradient_wire": main.get("gradient_wire"),
+                       "replicas": world if not wide else None, "l2": l2},
             "roofline": main["roofline"], "cpu_baseline": cpu, "e2e": main["e2e"],
             "gpu_launches": main["gpu_launches"],
             "clocks": sampler.summary({args.workload, args.workload + ":roofline", args.workload + ":e2e"}),
@@ -679,11 +683,15 @@ def main():
                     help="element type of the pinned host rows of the e2e leg (u8 = IDX pixel bytes / 255)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
                     help="operand type of the tensor-core workloads c4 / c5")
+    ap.add_argument("--wire", default="fp32", choices=["fp32", "bf16"],
+                    help="data-parallel gradient exchange format (bf16 = B2NN_FLAG_BF16_WIRE, opt-in: see dp_check.rel)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the side measurements (c5, TF32, the FP64 configs)")
     ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s back-to-back leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.wire == "bf16":
+        os.environ["B2NN_BENCH_WIRE"] = "bf16"
     if args.impl == "reference":
         run_reference(args)
     else:

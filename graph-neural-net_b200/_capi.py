@@ -12,7 +12,7 @@ OK = 0
 ERR_INVALID_ARG, ERR_DIM_MISMATCH, ERR_UNSUPPORTED, ERR_CUDA, ERR_NCCL, ERR_OOM, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6, -7
 NET_SOFTMAX_CE, NET_GENERAL = 0, 1
 PREC_F64, PREC_BF16, PREC_TF32 = 0, 1, 2
-FLAG_SCALED_INIT, FLAG_STABLE_SOFTMAX = 1, 2
+FLAG_SCALED_INIT, FLAG_STABLE_SOFTMAX, FLAG_BF16_WIRE = 1, 2, 4
 DT_F64, DT_F32, DT_BF16, DT_U8 = 0, 1, 2, 3
 DATA_DEVICE, DATA_HOST_PINNED = 0, 1
 

@@ -84,6 +84,7 @@ struct WideLayer {
     float *w = nullptr;         // FP32 master [in][ld_n]
     float *v = nullptr;         // FP32 velocity [in][ld_n]
     float *g = nullptr;         // FP32 summed gradient [in][ld_n]
+    __nv_bfloat16 *gb = nullptr;  // BF16 [in][ld_n]: the summed gradient as it travels with B2NN_FLAG_BF16_WIRE (else null)
     __nv_bfloat16 *wn = nullptr;  // BF16 [in][ld_n]: GEMM operand copy (MN-major B forward, K-major B delta); null for TF32 nets
     CUtensorMap tm_w;             // box map over wn (BF16 nets) or over w itself (TF32 nets), read K-major (delta GEMM)
     CUtensorMap tm_w_mn;          // the map the forward GEMM reads it MN-major with (TF32: 32-byte-atom swizzle; BF16: == tm_w)

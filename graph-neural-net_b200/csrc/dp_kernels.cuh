@@ -55,6 +55,8 @@ struct Args {
     float scale, momentum;
     unsigned int seq;           // handshake sequence number, identical on all ranks for this launch
     int f32_operand;            // TF32 nets: replicate the FP32 weights themselves (no BF16 copy exists)
+    int g_bf16;                 // B2NN_FLAG_BF16_WIRE: the per-GPU gradients are BF16 arrays at off_gb (2 B per parameter and peer)
+    unsigned long long off_gb;
     unsigned long long timeout_ns;  // bound of every cross-GPU wait
 };
 
@@ -93,6 +95,20 @@ __device__ __forceinline__ bool wait_flag_sys(const unsigned int *p, unsigned in
     while (ld_acquire_sys(p) != want)
         if (globaltimer_ns() - t0 > timeout_ns) return false;
     return true;
+}
+// 8 bytes = four BF16 gradients summed over every GPU of the team inside the switch (FP32 accumulation, BF16 result)
+__device__ __forceinline__ uint2 multimem_ld_reduce_add_bf16x4(const void *mc_addr) {
+    uint2 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0, %1}, [%2];"
+                 : "=r"(v.x), "=r"(v.y)
+                 : "l"(mc_addr)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 bf16x4_to_float4(uint2 u) {
+    const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
+    const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
+    return make_float4(lo.x, lo.y, hi.x, hi.y);
 }
 // 16 bytes (four FP32) replicated into every GPU of the team by the switch
 __device__ __forceinline__ void multimem_st_f32x4(void *mc_addr, float4 v) {
@@ -148,6 +164,35 @@ reduce_update_kernel(const Args a) {
         float4 g[UNROLL], wv[UNROLL], vv[UNROLL];
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.g_bf16) {
+            // BF16 wire: 8 bytes per owned float4 and rank (summed in FP32 here, or in the switch with a BF16 result)
+            if (a.mc != nullptr) {
+                const uint2 *gm = reinterpret_cast<const uint2 *>(a.mc + a.off_gb);
+#pragma unroll
+                for (int u = 0; u < UNROLL; u++) {
+                    const long long q = q0 + u * stride;
+                    if (q < hi) g[u] = bf16x4_to_float4(multimem_ld_reduce_add_bf16x4(gm + q));
+                }
+            } else {
+#pragma unroll
+                for (int p = 0; p < DP_MAX_WORLD; p++) {
+                    if (p < a.world) {
+                        const uint2 *gp = reinterpret_cast<const uint2 *>(a.arena[p] + a.off_gb);
+                        uint2 t[UNROLL];
+#pragma unroll
+                        for (int u = 0; u < UNROLL; u++) {
+                            const long long q = q0 + u * stride;
+                            t[u] = q < hi ? __ldcg(gp + q) : make_uint2(0u, 0u);
+                        }
+#pragma unroll
+                        for (int u = 0; u < UNROLL; u++) {
+                            const float4 f = bf16x4_to_float4(t[u]);
+                            g[u].x += f.x; g[u].y += f.y; g[u].z += f.z; g[u].w += f.w;
+                        }
+                    }
+                }
+            }
+        } else
         if (a.mc != nullptr) {
             // in-switch reduction: ONE load per owned float4, the NVSwitch gathers and adds the G copies
             const float4 *gm = reinterpret_cast<const float4 *>(a.mc + a.off_g);

@@ -83,7 +83,8 @@ enum EpiKind {
     EPI_LOGITS = 1,     // store FP32 acc to out0[M][ld0]
     EPI_DX = 2,         // d = acc * f'(from stored activation aux[M][ldaux]): store out0 in the operand type
     EPI_DW_UPDATE = 3,  // v = s*acc + mu*v; w -= v (FP32 master w,v [M][ldw]); BF16 copy of w to out0
-    EPI_DW_STORE = 4    // store FP32 acc (the summed gradient) to w[M][ldw]
+    EPI_DW_STORE = 4,   // store FP32 acc (the summed gradient) to w[M][ldw]
+    EPI_DW_STORE_BF16 = 5  // store the summed gradient rounded to BF16 to out0[M][ld0] (B2NN_FLAG_BF16_WIRE)
 };
 
 enum ActKind { ACT_LEAKY_RELU = 0, ACT_SIGMOID = 1, ACT_RELU = 2, ACT_TANH = 3, ACT_IDENTITY = 4 };
@@ -310,6 +311,11 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
                 }
             }
         }
+        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else if constexpr (EPI == EPI_DW_STORE_BF16) {
+        float x[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[c] = __uint_as_float(r[c]);
         store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else {  // EPI_DW_STORE
         store_f32_row(g.w, g.ldw, g.N, m, n0, r);

@@ -125,6 +125,10 @@ static int prof_end(cudaStream_t st, const ProfPair &pp) {
 }
 
 static inline bool is_tf32(const b2nn_net *net) { return net->precision == B2NN_PREC_TF32; }
+// B2NN_FLAG_BF16_WIRE: per-GPU gradients stored and exchanged as BF16 (BF16 nets, fused exchange only)
+static inline bool bf16_wire(const b2nn_net *net) {
+    return (net->flags & B2NN_FLAG_BF16_WIRE) != 0 && net->precision == B2NN_PREC_BF16;
+}
 
 typedef void (*GemmKernel)(const CUtensorMap, const CUtensorMap, const GemmArgs);
 template <int EPI, bool A_MN, bool B_MN, bool TF32>
@@ -185,7 +189,7 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
 
 template <int EPI, bool A_MN, bool B_MN>
 static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
-    if constexpr (EPI != EPI_DW_UPDATE) {
+    if constexpr (EPI != EPI_DW_UPDATE && EPI != EPI_DW_STORE_BF16) {
         if (is_tf32(net)) return launch_gemm_t<EPI, A_MN, B_MN, true>(net, ta, tb, g);
     }
     return launch_gemm_t<EPI, A_MN, B_MN, false>(net, ta, tb, g);
@@ -298,7 +302,8 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         y.in = net->dims[l]; y.out = net->dims[l + 1];
         y.ld_n = pad8(y.out);
         const size_t nf = (size_t)y.in * y.ld_n;
-        bytes += 3 * up(nf * sizeof(float)) + (is_tf32(net) ? 0 : up(nf * sizeof(__nv_bfloat16)));
+        bytes += 3 * up(nf * sizeof(float)) + (is_tf32(net) ? 0 : up(nf * sizeof(__nv_bfloat16))) +
+                 (bf16_wire(net) ? up(nf * sizeof(__nv_bfloat16)) : 0);
     }
     B2_CHECK_CUDA(cudaMalloc(&net->arena, bytes));
     B2_CHECK_CUDA(cudaMemset(net->arena, 0, bytes));
@@ -310,6 +315,7 @@ int wide_init(b2nn_net *net, const std::vector<double> &w_host) {
         y.g = (float *)(net->arena + off); off += up(nf * sizeof(float));
         y.w = (float *)(net->arena + off); off += up(nf * sizeof(float));
         y.v = (float *)(net->arena + off); off += up(nf * sizeof(float));
+        if (bf16_wire(net)) { y.gb = (__nv_bfloat16 *)(net->arena + off); off += up(nf * sizeof(__nv_bfloat16)); }
         if (is_tf32(net)) {
             y.wn = nullptr;  // the FP32 master array is the operand
             B2_TRY(make_tmap(&y.tm_w, y.w, y.out, y.in, y.ld_n, true, false));
@@ -348,6 +354,7 @@ int wide_rebase_arena(b2nn_net *net, char *new_base) {
         y.g = (float *)(new_base + ((char *)y.g - old));
         y.w = (float *)(new_base + ((char *)y.w - old));
         y.v = (float *)(new_base + ((char *)y.v - old));
+        if (y.gb) y.gb = (__nv_bfloat16 *)(new_base + ((char *)y.gb - old));
         if (y.wn) {
             y.wn = (__nv_bfloat16 *)(new_base + ((char *)y.wn - old));
             B2_TRY(make_tmap(&y.tm_w, y.wn, y.out, y.in, y.ld_n, false));
@@ -594,8 +601,15 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
         g.scale = scale; g.momentum = momentum;
         return launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g);
     }
-    g.w = y.g;
-    B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g)));
+    // BF16 wire (opt-in): the gradient leaves the epilogue as BF16 and the fused exchange reads 2 B per parameter
+    const bool wire16 = y.gb != nullptr && net->world > 1 && !net->peer_arena.empty();
+    if (wire16) {
+        g.out0 = y.gb; g.ld0 = y.ld_n;
+        B2_TRY((launch_gemm<EPI_DW_STORE_BF16, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g)));
+    } else {
+        g.w = y.g;
+        B2_TRY((launch_gemm<EPI_DW_STORE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g)));
+    }
     trace_mark(net, net->stream, "dW", l);
     if (us != net->stream) {
         B2_CHECK_CUDA(cudaEventRecord(net->layer_events[l], net->stream));
@@ -612,6 +626,8 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
         a.off_v = (unsigned long long)((char *)y.v - net->arena);
         a.off_wn = y.wn ? (unsigned long long)((char *)y.wn - net->arena) : 0ull;
         a.f32_operand = y.wn == nullptr;   // TF32 nets: the FP32 master array is the operand every rank reads
+        a.g_bf16 = wire16;
+        a.off_gb = wire16 ? (unsigned long long)((char *)y.gb - net->arena) : 0ull;
         a.timeout_ns = net->dp_timeout_ns;
         a.n4 = (long long)y.in * y.ld_n / 4;
         a.scale = scale; a.momentum = momentum;

@@ -80,8 +80,8 @@ enum b2nn_precision {
     B2NN_PREC_F64 = 0,  /* parity mode: double everywhere, like the JVM */
     B2NN_PREC_BF16 = 1, /* tcgen05 kind::f16 GEMMs, FP32 accumulate, FP32 master W and V */
     B2NN_PREC_TF32 = 2  /* tcgen05 kind::tf32 GEMMs over FP32 activations / deltas / master weights (no operand
-                         * copy), FP32 accumulate; data-parallel through the NCCL exchange only (the peer-memory
-                         * and multicast exports return UNSUPPORTED) */
+                         * copy), FP32 accumulate; data-parallel through the same exchanges as BF16 nets
+                         * (the fused kernel replicates the FP32 weights themselves) */
 };
 
 enum b2nn_flags {
@@ -90,7 +90,13 @@ enum b2nn_flags {
     B2NN_FLAG_SCALED_INIT = 1,
     /* subtract the row max inside softmax (mathematically identical; the
      * reference computes the max and never uses it, S:361-364). */
-    B2NN_FLAG_STABLE_SOFTMAX = 2
+    B2NN_FLAG_STABLE_SOFTMAX = 2,
+    /* data-parallel BF16 nets only: the per-GPU batch gradients travel as BF16 instead of FP32 (the gradient GEMM's
+     * epilogue stores BF16, the fused exchange kernel reads 2 B per parameter and peer instead of 4 and sums in FP32).
+     * Halves the exchange's wire and memory traffic; costs one BF16 rounding of every per-GPU gradient (and, with the
+     * in-switch reduction, of their sum): ~3e-3 relative on the update, above the 2e-3 bound the FP32 exchange is held
+     * to -- so it is opt-in, never the default.  Ignored by single-GPU nets and by the NCCL exchange. */
+    B2NN_FLAG_BF16_WIRE = 4
 };
 
 /* element type of dataset rows handed to b2nn_dataset_create.  B2NN_DT_U8 rows are IDX pixel bytes, read as

@@ -139,7 +139,7 @@ def gloo_init_comm_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-def nccl_worker(rank, world, port, out_dir, precision_name="bf16"):
+def nccl_worker(rank, world, port, out_dir, precision_name="bf16", extra_flags=0):
     """BF16 (or TF32) nets, one per GPU, stepping on their slice of each global batch with the per-layer NCCL
     all-reduce inside libb2nn.so; rank 0 also steps an un-sharded net on the whole global batch."""
     import torch
@@ -149,7 +149,7 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16"):
     g = ge.load_package()
     dims, gB, iters, step, mu = [256, 384, 128, 40], 256 * world, 6, 0.05, 0.9
     prec = g.capi.PREC_TF32 if precision_name == "tf32" else g.capi.PREC_BF16
-    flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX
+    flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX | extra_flags
     rng = np.random.RandomState(11)
     n_rows = 4 * gB
     x = rng.rand(n_rows, dims[0]).astype(np.float32)
@@ -171,7 +171,7 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16"):
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
         single = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=prec,
-                                                flags=flags, device=0)
+                                                flags=flags & ~g.capi.FLAG_BF16_WIRE, device=0)
         w0 = single.getWeights()
         for it in range(iters):
             single.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu)

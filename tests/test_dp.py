@@ -159,3 +159,30 @@ def test_two_nets_on_two_devices_in_one_process(g):
         assert np.isfinite(f64.getWeights()).all()
         f64.close()
     assert np.array_equal(out[0], out[2]) and np.array_equal(out[1], out[3])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("mode", ["p2p", "nvls"])
+def test_bf16_wire_exchange(g, tmp_path, mode, world, monkeypatch):
+    """B2NN_FLAG_BF16_WIRE (opt-in): the per-GPU gradients leave the gradient GEMM as BF16 and the fused exchange reads
+    2 B per parameter and peer.  Replicas stay bit-identical; against the single-GPU FP32-gradient run the update is off
+    by the BF16 rounding of each per-GPU gradient (and, in-switch, of their sum): bound 1e-2 of the update norm over 6
+    steps (measured ~3e-3, above the 2e-3 the FP32 exchange is held to -- which is why the flag is not the default)."""
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    if mode == "nvls" and _multicast_supported() is False:
+        pytest.skip("no NVSwitch multicast support on this box")
+    import torch.multiprocessing as mp
+    from tests import dp_workers
+    monkeypatch.setenv("B2NN_DP", mode)
+    mp.spawn(dp_workers.nccl_worker, args=(world, _free_port(), str(tmp_path), "bf16", g.capi.FLAG_BF16_WIRE),
+             nprocs=world, join=True)
+    r = np.load(tmp_path / "nccl.npz")
+    assert int(r["replicas_equal"]) == 1
+    du_dp, du_1 = r["w_dp"] - r["w0"], r["w_single"] - r["w0"]
+    rel = np.linalg.norm(du_dp - du_1) / np.linalg.norm(du_1)
+    print("bf16 wire", mode, world, "rel", rel)
+    assert 1e-5 < rel < 1e-2, rel          # really BF16 on the wire (an FP32 exchange lands at ~2e-4), and within the bound
+    assert str(r["mode"]) == mode
