@@ -39,7 +39,7 @@ void make_layout(const b2nn_net *net, int B, int G, Layout *out) {
     p.o_d3 = take(B * d3);
     p.o_t = take(2 * B * d3);
     p.o_misc = take(B);
-    p.o_a1o = take(B * p.nc0max);
+    p.o_a1o = take(2 * B * p.nc0max);   // double buffered by step parity
     p.o_part = take(16 * 4 * 4 + B * 4);  // KS*B <= max(NW*4, B) rows of 4
     p.o_w2t = take(d2 * d3);
     p.o_lut = take(256);

@@ -232,7 +232,8 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     double *w2t = sm + p.o_w2t;  // [d3][d2]
     double *z1o = sm + p.o_z1o;  // [B][nc0max] own pre-activations
     double *d1o = sm + p.o_d1o;  // [B][nc0max] own deltas
-    double *a1o = sm + p.o_a1o;  // [B][nc0max] own activations f(z1)
+    double *a1o_buf = sm + p.o_a1o;  // [2][B][nc0max] own activations f(z1), double buffered by step parity (the W1-row
+                                     // update of step it runs under barrier 1 of step it + 1, after phase 1 has written the next)
     double *part = sm + p.o_part;  // [KS][B][4] chunk sums of the blocked dot products
     const int KS = fused_ksplit(B, NW);
     double *z3 = sm + p.o_z3;    // [B][d3]  (reused for exp terms / loss terms)
@@ -276,8 +277,49 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     if (p.prof != nullptr && c == 0 && tid == 0)
         for (int i = 0; i < 16; i++) profs[i] = 0ULL;
     long long tprev_ = clock64();
+    // ---- the W1 / W2 updates of a step (phase 5b) -- deferred: they run under the barrier-1 wait of the NEXT step (their
+    // results are first needed by phase 2 / 3 / 4, all behind that barrier), or after the loop for the last step.
+    // Inputs: dl2, a1, dl3, a2 of the step (untouched until phases 2 / 3 of the next one) and its a1o buffer.
+    auto update_w1_w2 = [&](const double *a1o) {
+        // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
+        for (int kk = 0; kk < nc1; kk++)
+            for (int j = tid; j < d1; j += NT) {
+                double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
+                const double vprev = *vp;
+                double g = 0.0;
+                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k0 + kk], a1[(size_t)b * d1 + j]));
+                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+                w1c[kk * d1 + j] = __dsub_rn(w1c[kk * d1 + j], adj);
+                *vp = adj;
+            }
+        // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
+        for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
+            const int jj = e / d2, k = e - jj * d2;
+            double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
+            const double vprev = *vp;
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a1o[b * ncm + jj]));
+            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+            w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
+            *vp = adj;
+        }
+        // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
+        for (int e = tid; e < d2 * d3; e += NT) {
+            const int i = e / d3, j = e - i * d3;
+            const double vprev = v2[e];
+            double g = 0.0;
+            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl3[b * d3 + j], a2[b * d2 + i]));
+            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
+            const double wn = __dsub_rn(w2[e], adj);
+            w2[e] = wn;
+            w2t[j * d2 + i] = wn;
+            v2[e] = adj;
+        }
+    };
+
     for (int it = 0; it < p.iters; it++) {
         const int32_t *idx = p.idx + (size_t)it * B;
+        double *a1o = a1o_buf + (size_t)(it & 1) * B * ncm;
         double *z1pub = p.z1buf + (size_t)(it & 1) * B * d1;
         double *z2pub = p.z2buf + (size_t)(it & 1) * B * d2;
 
@@ -349,6 +391,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         // thread 0 waits for the other CTAs
         grid_barrier_overlap(p.bar, bar_target, gave_up, [&] {
             if (p.bulk && u8 && warp == 1 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar, lane);
+            if (it > 0) update_w1_w2(a1o_buf + (size_t)((it - 1) & 1) * B * ncm);   // phase 5b of the previous step
         });
         K1_MARK(2)  // barrier 1
 
@@ -548,46 +591,15 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             __syncthreads();
             if (warp == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar, lane);
         }
-        // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
-        for (int kk = 0; kk < nc1; kk++)
-            for (int j = tid; j < d1; j += NT) {
-                double *vp = p.V1 + (size_t)j * d2 + k0 + kk;
-                const double vprev = *vp;
-                double g = 0.0;
-                for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k0 + kk], a1[(size_t)b * d1 + j]));
-                const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
-                w1c[kk * d1 + j] = __dsub_rn(w1c[kk * d1 + j], adj);
-                *vp = adj;
-            }
-        K1_MARK(13)
-        // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
-        for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
-            const int jj = e / d2, k = e - jj * d2;
-            double *vp = p.V1b + (size_t)(j0 + jj) * d2 + k;
-            const double vprev = *vp;
-            double g = 0.0;
-            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl2[b * d2 + k], a1o[b * ncm + jj]));
-            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
-            w1r[jj * d2 + k] = __dsub_rn(w1r[jj * d2 + k], adj);
-            *vp = adj;
-        }
-        K1_MARK(14)
-        // W2 (replicated): g = sum_b delta3[b][j] * a2[b][i]
-        for (int e = tid; e < d2 * d3; e += NT) {
-            const int i = e / d3, j = e - i * d3;
-            const double vprev = v2[e];
-            double g = 0.0;
-            for (int b = 0; b < B; b++) g = __dadd_rn(g, __dmul_rn(dl3[b * d3 + j], a2[b * d2 + i]));
-            const double adj = sgd_adj(p.step, g, B, invB, p.momentum, vprev);
-            const double wn = __dsub_rn(w2[e], adj);
-            w2[e] = wn;
-            w2t[j * d2 + i] = wn;
-            v2[e] = adj;
-        }
+        // (phase 5b, the W1 / W2 updates, runs under barrier 1 of the next step: see update_w1_w2)
         __syncthreads();
         K1_MARK(7)  // phase 5
     }
 
+    if (p.iters > 0) {
+        update_w1_w2(a1o_buf + (size_t)((p.iters - 1) & 1) * B * ncm);
+        __syncthreads();
+    }
     if (p.prof != nullptr && c == 0 && tid == 0)
         for (int i = 0; i < 16; i++) p.prof[i] = profs[i];
     // ---- write the CTA's slices back to the canonical [in][out] state ----
