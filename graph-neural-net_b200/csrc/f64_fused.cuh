@@ -497,6 +497,25 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 for (int k = 0; k < d3; k++) sacc = __dadd_rn(sacc, __dmul_rn(w2t[(size_t)k * d2 + j], d3r[k]));
                 d2r[j] = __dmul_rn(sacc, d2r[j]);
             }
+            __syncwarp();
+            // phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own); lanes stride over k
+            {
+                double acc[FUSED_CMAX];
+#pragma unroll
+                for (int jj = 0; jj < FUSED_CMAX; jj++) acc[jj] = 0.0;
+                for (int k = lane; k < d2; k += 32) {
+                    const double dv = d2r[k];
+#pragma unroll
+                    for (int jj = 0; jj < FUSED_CMAX; jj++)
+                        if (jj < nc0) acc[jj] = fma(w1r[(size_t)jj * d2 + k], dv, acc[jj]);
+                }
+#pragma unroll
+                for (int jj = 0; jj < FUSED_CMAX; jj++) {
+                    const double sum = warp_sum_d(acc[jj]);
+                    if (lane == jj && jj < nc0)
+                        d1o[b * ncm + jj] = __dmul_rn(sum, act_prime(IACT, p.inner_p, z1o[b * ncm + jj]));
+                }
+            }
         }
         __syncthreads();
         if (p.loss_out && c == 0 && tid == 0) {   // the batch sum in ascending b: the order of a single serial loop
@@ -506,21 +525,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
 
         K1_MARK(5)  // phase 3
-        // ---- phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own) ----
-        for (int e = tid; e < B * nc0; e += NT) {
-            const int b = e / nc0, jj = e - b * nc0;
-            const double *wr = w1r + (size_t)jj * d2, *dr = dl2 + (size_t)b * d2;
-            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-            int k = 0;
-            for (; k + 3 < d2; k += 4) {
-                s0 = fma(wr[k], dr[k], s0); s1 = fma(wr[k + 1], dr[k + 1], s1);
-                s2 = fma(wr[k + 2], dr[k + 2], s2); s3 = fma(wr[k + 3], dr[k + 3], s3);
-            }
-            for (; k < d2; k++) s0 = fma(wr[k], dr[k], s0);
-            d1o[b * ncm + jj] = __dmul_rn((s0 + s1) + (s2 + s3), act_prime(IACT, p.inner_p, z1o[b * ncm + jj]));
-        }
-        __syncthreads();
-
+        // (phase 4, delta1 for the CTA's own columns, is the tail of the per-row chain above)
         K1_MARK(6)  // phase 4
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]
