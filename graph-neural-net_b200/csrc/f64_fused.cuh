@@ -427,105 +427,125 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         K1_MARK(4)  // barrier 2
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
-        // One WARP per batch row, start to end: the row's five small passes (100 + 10 + 10 + 10 + 100 values for C2) are
-        // chained with __syncwarp only -- as block-wide passes they cost five __syncthreads and left most threads idle
-        // (8.1 K cycles per step; profiles/r02_notes.md).  Every CTA runs the same code on the same inputs, so the
-        // replicas stay bit-identical; sums over the output layer keep the reference's ascending order.
-        for (int b = warp; b < B; b += NW) {
-            double *a2r = a2 + (size_t)b * d2, *d2r = dl2 + (size_t)b * d2;
-            double *z3r = z3 + (size_t)b * d3, *d3r = dl3 + (size_t)b * d3;
-            const double *ttr = tt + (size_t)b * d3;
-            for (int j = lane; j < d2; j += 32) {
-                const double q = __ldcg(z2pub + (size_t)b * d2 + j);
-                d2r[j] = act_prime(IACT, p.inner_p, q);  // f'(z2), multiplied into delta2 below
-                a2r[j] = act(IACT, p.inner_p, q);
-            }
-            __syncwarp();
-            // z3[b][j] = sum_k a2[b][k] W2[k][j]: lanes stride over k, eight outputs at a time, one xor tree per output
-            for (int jb = 0; jb < d3; jb += 8) {
-                double acc[8];
+        {
+            const int n = B * d2;
+            constexpr int ZL = 4;
+            for (int e0 = tid; e0 < n; e0 += ZL * NT) {
+                double q[ZL];
 #pragma unroll
-                for (int u = 0; u < 8; u++) acc[u] = 0.0;
-                for (int k = lane; k < d2; k += 32) {
-                    const double av = a2r[k];
+                for (int u = 0; u < ZL; u++) q[u] = (e0 + u * NT < n) ? __ldcg(z2pub + e0 + u * NT) : 0.0;
 #pragma unroll
-                    for (int u = 0; u < 8; u++)
-                        if (jb + u < d3) acc[u] = fma(av, w2t[(size_t)(jb + u) * d2 + k], acc[u]);
-                }
-#pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    const double sum = warp_sum_d(acc[u]);
-                    if (lane == u && jb + u < d3) z3r[jb + u] = sum;
-                }
-            }
-            __syncwarp();
-            if (p.kind == 0) {
-                // softmax (S:357-376) + cross entropy (S:213-217) + delta (S:249-251)
-                double mx = 0.0;
-                if (p.stable) {
-                    mx = z3r[0];
-                    for (int j = 1; j < d3; j++) mx = fmax(mx, z3r[j]);
-                }
-                __syncwarp();
-                for (int j = lane; j < d3; j += 32) z3r[j] = exp(z3r[j] - mx);
-                __syncwarp();
-                double sum = 0.0;
-                for (int j = 0; j < d3; j++) sum = __dadd_rn(sum, z3r[j]);  // ascending i like the reference (every lane)
-                __syncwarp();
-                for (int j = lane; j < d3; j += 32) {
-                    const double pr = __ddiv_rn(z3r[j], sum);
-                    d3r[j] = __dsub_rn(pr, ttr[j]);
-                    if (p.loss_out) z3r[j] = __dmul_rn(ttr[j], log(pr));
-                }
-            } else {
-                // general output layer (G:268-271, G:236-239)
-                for (int j = lane; j < d3; j += 32) {
-                    const double z = z3r[j], av = act(p.last_act, p.last_p, z);
-                    d3r[j] = __dmul_rn(loss_prime(p.loss_kind, av, ttr[j]), act_prime(p.last_act, p.last_p, z));
-                    if (p.loss_out) z3r[j] = -loss_fn(p.loss_kind, av, ttr[j]);
-                }
-            }
-            __syncwarp();
-            if (p.loss_out && c == 0 && lane == 0) {
-                double l = 0.0;   // per-row loss in ascending j
-                for (int j = 0; j < d3; j++) l = __dsub_rn(l, z3r[j]);
-                misc[b] = l;
-            }
-            // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
-            for (int j = lane; j < d2; j += 32) {
-                double sacc = 0.0;
-                for (int k = 0; k < d3; k++) sacc = __dadd_rn(sacc, __dmul_rn(w2t[(size_t)k * d2 + j], d3r[k]));
-                d2r[j] = __dmul_rn(sacc, d2r[j]);
-            }
-            __syncwarp();
-            // phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own); lanes stride over k
-            {
-                double acc[FUSED_CMAX];
-#pragma unroll
-                for (int jj = 0; jj < FUSED_CMAX; jj++) acc[jj] = 0.0;
-                for (int k = lane; k < d2; k += 32) {
-                    const double dv = d2r[k];
-#pragma unroll
-                    for (int jj = 0; jj < FUSED_CMAX; jj++)
-                        if (jj < nc0) acc[jj] = fma(w1r[(size_t)jj * d2 + k], dv, acc[jj]);
-                }
-#pragma unroll
-                for (int jj = 0; jj < FUSED_CMAX; jj++) {
-                    const double sum = warp_sum_d(acc[jj]);
-                    if (lane == jj && jj < nc0)
-                        d1o[b * ncm + jj] = __dmul_rn(sum, act_prime(IACT, p.inner_p, z1o[b * ncm + jj]));
-                }
+                for (int u = 0; u < ZL; u++)
+                    if (e0 + u * NT < n) {
+                        dl2[e0 + u * NT] = act_prime(IACT, p.inner_p, q[u]);  // f'(z2), multiplied into delta2 below
+                        a2[e0 + u * NT] = act(IACT, p.inner_p, q[u]);
+                    }
             }
         }
         __syncthreads();
-        if (p.loss_out && c == 0 && tid == 0) {   // the batch sum in ascending b: the order of a single serial loop
-            double tot = 0.0;
-            for (int b = 0; b < B; b++) tot = __dadd_rn(tot, misc[b]);
-            p.loss_out[it] = tot;
+        K1_MARK(8)
+        for (int e = tid; e < B * d3; e += NT) {
+            const int b = e / d3, j = e - b * d3;
+            const double *ar = a2 + (size_t)b * d2;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int k = 0;
+            for (; k + 3 < d2; k += 4) {
+                s0 = fma(ar[k], w2[k * d3 + j], s0);
+                s1 = fma(ar[k + 1], w2[(k + 1) * d3 + j], s1);
+                s2 = fma(ar[k + 2], w2[(k + 2) * d3 + j], s2);
+                s3 = fma(ar[k + 3], w2[(k + 3) * d3 + j], s3);
+            }
+            for (; k < d2; k++) s0 = fma(ar[k], w2[k * d3 + j], s0);
+            z3[e] = (s0 + s1) + (s2 + s3);
         }
+        __syncthreads();
+        K1_MARK(9)
+        if (p.kind == 0) {
+            // softmax (S:357-376) + cross entropy (S:213-217) + delta (S:249-251)
+            if (tid < B) {
+                double mx = 0.0;
+                if (p.stable) {
+                    mx = z3[tid * d3];
+                    for (int j = 1; j < d3; j++) mx = fmax(mx, z3[tid * d3 + j]);
+                }
+                misc[tid] = mx;
+            }
+            __syncthreads();
+            for (int e = tid; e < B * d3; e += NT) z3[e] = exp(z3[e] - misc[e / d3]);
+            __syncthreads();
+            if (tid < B) {
+                double sum = 0.0;
+                for (int j = 0; j < d3; j++) sum = __dadd_rn(sum, z3[tid * d3 + j]);  // ascending i like the reference
+                misc[tid] = sum;
+            }
+            __syncthreads();
+            for (int e = tid; e < B * d3; e += NT) {
+                const double pr = __ddiv_rn(z3[e], misc[e / d3]);
+                dl3[e] = __dsub_rn(pr, tt[e]);
+                if (p.loss_out) z3[e] = __dmul_rn(tt[e], log(pr));
+            }
+        } else {
+            // general output layer (G:268-271, G:236-239)
+            for (int e = tid; e < B * d3; e += NT) {
+                const double z = z3[e], a = act(p.last_act, p.last_p, z);
+                dl3[e] = __dmul_rn(loss_prime(p.loss_kind, a, tt[e]), act_prime(p.last_act, p.last_p, z));
+                if (p.loss_out) z3[e] = -loss_fn(p.loss_kind, a, tt[e]);
+            }
+        }
+        __syncthreads();
+        K1_MARK(10)
+        if (p.loss_out && c == 0) {
+            // per-row loss in ascending j (one thread per row), then the batch sum in ascending b: the same
+            // order of additions as a single serial loop
+            if (tid < B) {
+                double l = 0.0;
+                for (int j = 0; j < d3; j++) l = __dsub_rn(l, z3[tid * d3 + j]);
+                misc[tid] = l;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                double tot = 0.0;
+                for (int b = 0; b < B; b++) tot = __dadd_rn(tot, misc[b]);
+                p.loss_out[it] = tot;
+            }
+        }
+        K1_MARK(11)
+        // delta2 = (W2 delta3) (.) f'(z2), ascending k like S:274-277
+        for (int b = warp; b < B; b += NW)
+            for (int jb = lane; jb < d2; jb += 128) {  // four columns per lane: four independent addition chains
+                double s4[4] = {0.0, 0.0, 0.0, 0.0};
+                for (int k = 0; k < d3; k++) {
+                    const double dk = dl3[b * d3 + k];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const int j = jb + 32 * q;
+                        if (j < d2) s4[q] = __dadd_rn(s4[q], __dmul_rn(w2t[k * d2 + j], dk));
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int j = jb + 32 * q;
+                    if (j < d2) dl2[b * d2 + j] = __dmul_rn(s4[q], dl2[b * d2 + j]);
+                }
+            }
+        __syncthreads();
 
         K1_MARK(5)  // phase 3
-        // (phase 4, delta1 for the CTA's own columns, is the tail of the per-row chain above)
+        // ---- phase 4: delta1 for the CTA's own columns: (W1[own rows] delta2) (.) f'(z1 own) ----
+        for (int e = tid; e < B * nc0; e += NT) {
+            const int b = e / nc0, jj = e - b * nc0;
+            const double *wr = w1r + (size_t)jj * d2, *dr = dl2 + (size_t)b * d2;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int k = 0;
+            for (; k + 3 < d2; k += 4) {
+                s0 = fma(wr[k], dr[k], s0); s1 = fma(wr[k + 1], dr[k + 1], s1);
+                s2 = fma(wr[k + 2], dr[k + 2], s2); s3 = fma(wr[k + 3], dr[k + 3], s3);
+            }
+            for (; k < d2; k++) s0 = fma(wr[k], dr[k], s0);
+            d1o[b * ncm + jj] = __dmul_rn((s0 + s1) + (s2 + s3), act_prime(IACT, p.inner_p, z1o[b * ncm + jj]));
+        }
+        __syncthreads();
+
         K1_MARK(6)  // phase 4
         // ---- phase 5: gradients (batch order, un-fused multiply/add like S:281 + S:309-317) and updates ----
         // W0[:, own]: g = sum_b delta1[b][jj] * a0[b][k]

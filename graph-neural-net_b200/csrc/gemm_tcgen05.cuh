@@ -8,10 +8,9 @@
 // tcgen05.mma.cta_group::2): a pair owns a 256 x 256 output tile, each CTA stages ITS 128 rows of A and
 // ITS 128 rows of B per 64-deep K block, the leader's single MMA thread drives both tensor cores, and each
 // CTA's TMEM receives its 128 accumulator rows.
-//   warp 0      TMA producer   : cp.async.bulk.tensor, 64x64 128B-swizzled boxes, 5-stage 32 KB ring
+//   warp 0      TMA producer   : cp.async.bulk.tensor, 64x64 128B-swizzled boxes, 6-stage 32 KB ring
 //   warp 1      MMA issuer     : leader CTA only; M=256, N=256 (or 128), K=16 per instruction
-//   warps 2..9  epilogue       : tcgen05.ld 32x32b -> registers -> shared-memory staging -> fused epilogue -> global
-//                                (row-major, whole 128-byte row segments per warp access)
+//   warps 2..9  epilogue       : tcgen05.ld 32x32b -> registers -> fused epilogue -> global (row-major)
 // Pipelines: smem full/empty ring and a double-buffered TMEM accumulator (2 x 256 columns) so the epilogue
 // of tile i overlaps the main loop of tile i+1.
 //
@@ -47,12 +46,7 @@ namespace b2nn {
 constexpr int GEMM_BM = 128;        // rows of A per CTA (pair tile: 256)
 constexpr int GEMM_BN = 256;        // pair tile width
 constexpr int GEMM_BK = 64;         // 64 bf16 = 128 B = one swizzle row (BF16 operands; GemmCfg<true> for TF32)
-#ifndef B2NN_GEMM_STAGES
-#define B2NN_GEMM_STAGES 5
-#endif
-constexpr int GEMM_STAGES = B2NN_GEMM_STAGES;   // 5 x 32 KB operand stages + 32 KB of epilogue staging = the 198 KB footprint the
-                                                // 6-stage kernel had: the side-stream kernels (update, exchange, input prologue)
-                                                // still find shared memory on the same SM and run beside the GEMM CTA
+constexpr int GEMM_STAGES = 6;
 #ifndef B2NN_GEMM_EPI_WARPS
 #define B2NN_GEMM_EPI_WARPS 8
 #endif
@@ -65,12 +59,7 @@ constexpr int GEMM_CHUNK_BYTES = 64 * GEMM_BK * 2;      // one 64 x 64 TMA box: 
 constexpr int GEMM_A_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of A
 constexpr int GEMM_B_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of B (64 for a half tile)
 constexpr int GEMM_STAGE_BYTES = GEMM_A_BYTES + GEMM_B_BYTES;
-// Epilogue staging: 4 KB per epilogue warp (32 accumulator rows x 32 FP32 columns), so that the warp can hand the chunk to
-// global memory as whole row segments (see epilogue_quad)
-constexpr int GEMM_EPI_STAGE_BYTES = 32 * 128;
-constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers, item ring*/ +
-                                GEMM_EPI_WARPS * GEMM_EPI_STAGE_BYTES;
-static_assert(GEMM_SMEM_BYTES + 1024 <= 232448, "shared memory of one CTA (227 KB incl. the 1 KB the system reserves)");
+constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers, item ring*/;
 constexpr uint32_t GEMM_TMEM_COLS = 512;  // 2 accumulators x 256 fp32 columns
 constexpr int GEMM_SCHED_SLOTS = 4;       // depth of the work-item ring between the scheduler and the role warps
 constexpr int GEMM_SCHED_READERS = 2 /*producers*/ + 1 /*MMA*/ + 2 * GEMM_EPI_WARPS;
@@ -143,122 +132,194 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return *reinterpret_cast<uint32_t *>(&t);
 }
 
-// ---- fused epilogues on FOUR consecutive columns of one output row -------------------------------------------------
-// The accumulator arrives one ROW per thread (tcgen05.ld 32x32b: lane = row).  Stored that way, every 16-byte store of a
-// warp goes to a different row: 32 requests per instruction, and the epilogue of a tile costs 8-15 K cycles whatever the
-// number of warps (profiles/r02_notes.md).  So each warp first parks its 32 x 32 FP32 chunk in shared memory
-// (16-byte slots XOR-swizzled by row: conflict-free both ways) and reads it back with eight lanes per row: a warp-wide
-// access then covers four whole 128-byte row segments (64 bytes for BF16 outputs), and the arrays the epilogue READS
-// (the stored activation of EPI_DX, w / v of EPI_DW_UPDATE) are fetched the same coalesced way.
-template <int ACT>
-__device__ __forceinline__ float act_ct(float p, float z) {
-    if constexpr (ACT == ACT_LEAKY_RELU) return z > 0.f ? z : p * z;
-    else if constexpr (ACT == ACT_SIGMOID) return 1.f / (1.f + __expf(-z));
-    else if constexpr (ACT == ACT_RELU) return fmaxf(z, 0.f);
-    else if constexpr (ACT == ACT_TANH) return 1.f - 2.f / (1.f + __expf(2.f * z));  // tanh, BF16-accurate
-    else return z;
-}
-template <int ACT>
-__device__ __forceinline__ float act_prime_ct(float p, float a) {   // from the stored activation a = f(z)
-    if constexpr (ACT == ACT_LEAKY_RELU) return a > 0.f ? 1.f : p;
-    else if constexpr (ACT == ACT_SIGMOID) return a * (1.f - a);
-    else if constexpr (ACT == ACT_RELU) return a > 0.f ? 1.f : 0.f;
-    else if constexpr (ACT == ACT_TANH) return 1.f - a * a;
-    else return 1.f;
-}
-
-template <int EPI, bool TF32, int ACT>
-__device__ __forceinline__ void epilogue_quad(const GemmArgs &g, int m, int n, float4 acc) {
-    if (m >= g.M || n >= g.N) return;
-    const bool full = n + 4 <= g.N;
-    float x[4] = {acc.x, acc.y, acc.z, acc.w};
-    // ---- what to store ----
-    if constexpr (EPI == EPI_ACT) {
+// Store 32 consecutive values of row m as bf16.
+__device__ __forceinline__ void store_bf16_row(__nv_bfloat16 *o0, int ld0, int N, int m, int n0, const float (&x)[32]) {
+    __nv_bfloat16 *row = o0 + (size_t)m * ld0 + n0;
+    if (n0 + 32 <= N) {
 #pragma unroll
-        for (int c = 0; c < 4; c++) x[c] = act_ct<ACT>(g.act_param, x[c]);
-    } else if constexpr (EPI == EPI_DX) {
-        // d = acc * f'(a), f' from the STORED activation
-        float a[4] = {0.f, 0.f, 0.f, 0.f};
-        if constexpr (TF32) {
-            const float *ap = reinterpret_cast<const float *>(g.aux) + (size_t)m * g.ldaux + n;
-            if (full) { const float4 t = *reinterpret_cast<const float4 *>(ap); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
-            else for (int c = 0; n + c < g.N; c++) a[c] = ap[c];
-        } else {
-            const __nv_bfloat16 *ap = reinterpret_cast<const __nv_bfloat16 *>(g.aux) + (size_t)m * g.ldaux + n;
-            if (full) {
-                const uint2 t = *reinterpret_cast<const uint2 *>(ap);
-                const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&t.x));
-                const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&t.y));
-                a[0] = lo.x; a[1] = lo.y; a[2] = hi.x; a[3] = hi.y;
-            } else for (int c = 0; n + c < g.N; c++) a[c] = __bfloat162float(ap[c]);
-        }
-#pragma unroll
-        for (int c = 0; c < 4; c++) x[c] *= act_prime_ct<ACT>(g.act_param, a[c]);
-    } else if constexpr (EPI == EPI_DW_UPDATE) {
-        static_assert(!TF32 || EPI != EPI_DW_UPDATE, "the fused-update epilogue emits the BF16 operand copy; TF32 nets have none");
-        // momentum SGD fused into the gradient GEMM (SoftmaxCrossEntropyNeuralNet.java:325-342):
-        // adj = step*G/B + mu*prev ; W -= adj ; prev = adj.  G never reaches HBM.
-        float *wp = g.w + (size_t)m * g.ldw + n, *vp = g.v + (size_t)m * g.ldw + n;
-        if (full) {
-            float4 w4 = *reinterpret_cast<const float4 *>(wp), v4 = *reinterpret_cast<const float4 *>(vp);
-            v4.x = g.scale * x[0] + g.momentum * v4.x; v4.y = g.scale * x[1] + g.momentum * v4.y;
-            v4.z = g.scale * x[2] + g.momentum * v4.z; v4.w = g.scale * x[3] + g.momentum * v4.w;
-            w4.x -= v4.x; w4.y -= v4.y; w4.z -= v4.z; w4.w -= v4.w;
-            *reinterpret_cast<float4 *>(wp) = w4;
-            *reinterpret_cast<float4 *>(vp) = v4;
-            x[0] = w4.x; x[1] = w4.y; x[2] = w4.z; x[3] = w4.w;
-        } else {
-            for (int c = 0; n + c < g.N; c++) {
-                const float vn = g.scale * x[c] + g.momentum * vp[c];
-                const float wn = wp[c] - vn;
-                vp[c] = vn; wp[c] = wn; x[c] = wn;
-            }
-        }
-    }
-    // ---- where to store it ----
-    constexpr bool F32_OUT = EPI == EPI_LOGITS || EPI == EPI_DW_STORE || (TF32 && (EPI == EPI_ACT || EPI == EPI_DX));
-    if constexpr (F32_OUT) {
-        float *o = (EPI == EPI_DW_STORE) ? g.w + (size_t)m * g.ldw + n : reinterpret_cast<float *>(g.out0) + (size_t)m * g.ld0 + n;
-        if (full) *reinterpret_cast<float4 *>(o) = make_float4(x[0], x[1], x[2], x[3]);
-        else for (int c = 0; n + c < g.N; c++) o[c] = x[c];
-    } else {  // BF16: activations, deltas, the operand copy of the fused update, the BF16-wire gradient
-        __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(g.out0) + (size_t)m * g.ld0 + n;
-        if (full) *reinterpret_cast<uint2 *>(o) = make_uint2(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]));
-        else for (int c = 0; n + c < g.N; c++) o[c] = __float2bfloat16_rn(x[c]);
-    }
-}
-
-// one 32-row x 32-column accumulator chunk of this warp: r = row `lane`; m_base / n_base = its first row / column
-template <int EPI, bool TF32, int ACT>
-__device__ __forceinline__ void epilogue_readback(const GemmArgs &g, const float4 *stage, int lane, int m_base, int n_base) {
-    const int slot = lane & 7;
-#pragma unroll 4
-    for (int i = 0; i < 8; i++) {
-        const int row = 4 * i + (lane >> 3);
-        const float4 acc = stage[row * 8 + (slot ^ (row & 7))];
-        epilogue_quad<EPI, TF32, ACT>(g, m_base + row, n_base + 4 * slot, acc);
-    }
-}
-template <int EPI, bool TF32>
-__device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, float4 *stage, int lane, int m_base, int n_base,
-                                               const uint32_t (&r)[32]) {
-#pragma unroll
-    for (int q = 0; q < 8; q++)
-        stage[lane * 8 + (q ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                                                          __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
-    __syncwarp();
-    if constexpr (EPI == EPI_ACT || EPI == EPI_DX) {
-        switch (g.act) {   // one branch per chunk, not per element
-        case ACT_LEAKY_RELU: epilogue_readback<EPI, TF32, ACT_LEAKY_RELU>(g, stage, lane, m_base, n_base); break;
-        case ACT_SIGMOID: epilogue_readback<EPI, TF32, ACT_SIGMOID>(g, stage, lane, m_base, n_base); break;
-        case ACT_RELU: epilogue_readback<EPI, TF32, ACT_RELU>(g, stage, lane, m_base, n_base); break;
-        case ACT_TANH: epilogue_readback<EPI, TF32, ACT_TANH>(g, stage, lane, m_base, n_base); break;
-        default: epilogue_readback<EPI, TF32, ACT_IDENTITY>(g, stage, lane, m_base, n_base);
+        for (int q = 0; q < 4; q++) {
+            uint4 u;
+            u.x = pack_bf16x2(x[8 * q + 0], x[8 * q + 1]);
+            u.y = pack_bf16x2(x[8 * q + 2], x[8 * q + 3]);
+            u.z = pack_bf16x2(x[8 * q + 4], x[8 * q + 5]);
+            u.w = pack_bf16x2(x[8 * q + 6], x[8 * q + 7]);
+            reinterpret_cast<uint4 *>(row)[q] = u;
         }
     } else {
-        epilogue_readback<EPI, TF32, ACT_IDENTITY>(g, stage, lane, m_base, n_base);
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            if (n0 + c < N) row[c] = __float2bfloat16_rn(x[c]);
     }
-    __syncwarp();  // the chunk is out before the next one overwrites the staging rows
+}
+
+__device__ __forceinline__ void store_f32_row(float *base, int ld, int N, int m, int n0, const uint32_t (&r)[32]) {
+    float *row = base + (size_t)m * ld + n0;
+    if (n0 + 32 <= N) {
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            reinterpret_cast<float4 *>(row)[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                                             __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+    } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            if (n0 + c < N) row[c] = __uint_as_float(r[c]);
+    }
+}
+
+// Store 32 consecutive values of row m as fp32 (TF32 nets keep activations / deltas in FP32).
+__device__ __forceinline__ void store_f32_row(float *base, int ld, int N, int m, int n0, const float (&x)[32]) {
+    float *row = base + (size_t)m * ld + n0;
+    if (n0 + 32 <= N) {
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            reinterpret_cast<float4 *>(row)[q] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
+    } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++)
+            if (n0 + c < N) row[c] = x[c];
+    }
+}
+
+// x[c] = acc[c] * fprime(a[c]) for 32 columns, a unpacked from BF16 on the fly
+template <class F>
+__device__ __forceinline__ void dx32(const uint4 (&u)[4], const uint32_t (&r)[32], float (&x)[32], F fprime) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u[q]);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const float2 a = __bfloat1622float2(h[e]);
+            x[8 * q + 2 * e] = __uint_as_float(r[8 * q + 2 * e]) * fprime(a.x);
+            x[8 * q + 2 * e + 1] = __uint_as_float(r[8 * q + 2 * e + 1]) * fprime(a.y);
+        }
+    }
+}
+
+// the same for FP32 activations (TF32 nets)
+template <class F>
+__device__ __forceinline__ void dx32_f32(const float *arow, int n0, int N, const uint32_t (&r)[32], float (&x)[32], F fprime) {
+    if (n0 + 32 <= N) {
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const float4 a = reinterpret_cast<const float4 *>(arow)[q];
+            x[4 * q + 0] = __uint_as_float(r[4 * q + 0]) * fprime(a.x);
+            x[4 * q + 1] = __uint_as_float(r[4 * q + 1]) * fprime(a.y);
+            x[4 * q + 2] = __uint_as_float(r[4 * q + 2]) * fprime(a.z);
+            x[4 * q + 3] = __uint_as_float(r[4 * q + 3]) * fprime(a.w);
+        }
+    } else {
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[c] = (n0 + c < N) ? __uint_as_float(r[c]) * fprime(arow[c]) : 0.f;
+    }
+}
+
+template <int EPI, bool TF32>
+__device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0, const uint32_t (&r)[32]) {
+    if (m >= g.M || n0 >= g.N) return;
+    if constexpr (EPI == EPI_ACT) {
+        float x[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[c] = __uint_as_float(r[c]);
+        // branch on the activation once per 32 columns, not per element (fewer live registers)
+        switch (g.act) {
+        case ACT_LEAKY_RELU:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = x[c] > 0.f ? x[c] : g.act_param * x[c];
+            break;
+        case ACT_RELU:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = fmaxf(x[c], 0.f);
+            break;
+        case ACT_SIGMOID:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = 1.f / (1.f + __expf(-x[c]));
+            break;
+        case ACT_TANH:
+#pragma unroll
+            for (int c = 0; c < 32; c++) x[c] = 1.f - 2.f / (1.f + __expf(2.f * x[c]));  // tanh, BF16-accurate
+            break;
+        default: break;  // identity
+        }
+        if constexpr (TF32) store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, x);
+        else store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else if constexpr (EPI == EPI_LOGITS) {
+        store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, r);
+    } else if constexpr (EPI == EPI_DX && TF32) {
+        const float *arow = reinterpret_cast<const float *>(g.aux) + (size_t)m * g.ldaux + n0;
+        float x[32];
+        switch (g.act) {  // one branch per 32 columns; f' from the stored activation
+        case ACT_LEAKY_RELU: { const float p = g.act_param; dx32_f32(arow, n0, g.N, r, x, [p](float a) { return a > 0.f ? 1.f : p; }); break; }
+        case ACT_RELU: dx32_f32(arow, n0, g.N, r, x, [](float a) { return a > 0.f ? 1.f : 0.f; }); break;
+        case ACT_SIGMOID: dx32_f32(arow, n0, g.N, r, x, [](float a) { return a * (1.f - a); }); break;
+        case ACT_TANH: dx32_f32(arow, n0, g.N, r, x, [](float a) { return 1.f - a * a; }); break;
+        default: dx32_f32(arow, n0, g.N, r, x, [](float) { return 1.f; });
+        }
+        store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else if constexpr (EPI == EPI_DX) {
+        const __nv_bfloat16 *arow = reinterpret_cast<const __nv_bfloat16 *>(g.aux) + (size_t)m * g.ldaux + n0;
+        uint4 u[4];  // the 32 stored activations a = f(z), packed BF16
+        if (n0 + 32 <= g.N) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) u[q] = reinterpret_cast<const uint4 *>(arow)[q];
+        } else {
+            uint32_t *uw = reinterpret_cast<uint32_t *>(u);
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+                const float lo = (n0 + c < g.N) ? __bfloat162float(arow[c]) : 0.f;
+                const float hi = (n0 + c + 1 < g.N) ? __bfloat162float(arow[c + 1]) : 0.f;
+                uw[c >> 1] = pack_bf16x2(lo, hi);
+            }
+        }
+        float x[32];
+        switch (g.act) {  // one branch per 32 columns; f' from the stored activation
+        case ACT_LEAKY_RELU: { const float p = g.act_param; dx32(u, r, x, [p](float a) { return a > 0.f ? 1.f : p; }); break; }
+        case ACT_RELU: dx32(u, r, x, [](float a) { return a > 0.f ? 1.f : 0.f; }); break;
+        case ACT_SIGMOID: dx32(u, r, x, [](float a) { return a * (1.f - a); }); break;
+        case ACT_TANH: dx32(u, r, x, [](float a) { return 1.f - a * a; }); break;
+        default: dx32(u, r, x, [](float) { return 1.f; });
+        }
+        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else if constexpr (EPI == EPI_DW_UPDATE) {
+        static_assert(!TF32, "the fused-update epilogue emits the BF16 operand copy; TF32 nets have none");
+        // momentum SGD fused into the gradient GEMM (SoftmaxCrossEntropyNeuralNet.java:325-342):
+        // adj = step*G/B + mu*prev ; W -= adj ; prev = adj.  G never reaches HBM.
+        float *wrow = g.w + (size_t)m * g.ldw + n0;
+        float *vrow = g.v + (size_t)m * g.ldw + n0;
+        float x[32];
+        if (n0 + 32 <= g.N) {
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                float4 w4 = reinterpret_cast<const float4 *>(wrow)[q];
+                float4 v4 = reinterpret_cast<const float4 *>(vrow)[q];
+                v4.x = g.scale * __uint_as_float(r[4 * q + 0]) + g.momentum * v4.x;
+                v4.y = g.scale * __uint_as_float(r[4 * q + 1]) + g.momentum * v4.y;
+                v4.z = g.scale * __uint_as_float(r[4 * q + 2]) + g.momentum * v4.z;
+                v4.w = g.scale * __uint_as_float(r[4 * q + 3]) + g.momentum * v4.w;
+                w4.x -= v4.x; w4.y -= v4.y; w4.z -= v4.z; w4.w -= v4.w;
+                reinterpret_cast<float4 *>(wrow)[q] = w4;
+                reinterpret_cast<float4 *>(vrow)[q] = v4;
+                x[4 * q + 0] = w4.x; x[4 * q + 1] = w4.y; x[4 * q + 2] = w4.z; x[4 * q + 3] = w4.w;
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+                x[c] = 0.f;
+                if (n0 + c < g.N) {
+                    float vn = g.scale * __uint_as_float(r[c]) + g.momentum * vrow[c];
+                    float wn = wrow[c] - vn;
+                    vrow[c] = vn; wrow[c] = wn; x[c] = wn;
+                }
+            }
+        }
+        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else if constexpr (EPI == EPI_DW_STORE_BF16) {
+        float x[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) x[c] = __uint_as_float(r[c]);
+        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
+    } else {  // EPI_DW_STORE
+        store_f32_row(g.w, g.ldw, g.N, m, n0, r);
+    }
 }
 
 // Work list of one launch: items [0, full) are 256 x 256 tiles in row-major tile order, items
@@ -331,7 +392,6 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     ring.sempty = ring.sfull + GEMM_SCHED_SLOTS;
     ring.sitem = reinterpret_cast<volatile uint32_t *>(ring.sempty + GEMM_SCHED_SLOTS);
     ring.sempty_rank1 = ptx::map_to_rank(ring.sempty, 1);
-    float4 *epi_stage_base = reinterpret_cast<float4 *>(smem + GEMM_STAGES * GEMM_STAGE_BYTES + 512);
     if (g.tile_counter == nullptr) { ring.static_next = (int)(blockIdx.x >> 1); ring.static_stride = (int)(gridDim.x >> 1); }
 
     const int warp = threadIdx.x >> 5;
@@ -498,8 +558,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             const uint32_t c1 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::tc_fence_after();
-            const int m_base = m0 + rank * GEMM_BM + q * 32;   // first of this warp's 32 rows (lane = row in TMEM)
-            float4 *stage = epi_stage_base + (size_t)(warp - 2) * (GEMM_EPI_STAGE_BYTES / 16);
+            const int m = m0 + rank * GEMM_BM + q * 32 + lane;
             const int cbeg = part * (bn / GEMM_EPI_PARTS), cend = cbeg + bn / GEMM_EPI_PARTS;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * GEMM_BN;
 #pragma unroll 1
@@ -507,7 +566,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
                 uint32_t r[32];
                 ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
                 ptx::tmem_ld_wait();
-                epilogue_chunk<EPI, TF32>(g, stage, lane, m_base, n0 + c0, r);
+                epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r);
             }
             ptx::tc_fence_before();
             __syncwarp();
