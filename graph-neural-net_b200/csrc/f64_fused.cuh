@@ -277,10 +277,11 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
     if (p.prof != nullptr && c == 0 && tid == 0)
         for (int i = 0; i < 16; i++) profs[i] = 0ULL;
     long long tprev_ = clock64();
-    // ---- the W1 / W2 updates of a step (phase 5b) -- deferred: they run under the barrier-1 wait of the NEXT step (their
-    // results are first needed by phase 2 / 3 / 4, all behind that barrier), or after the loop for the last step.
-    // Inputs: dl2, a1, dl3, a2 of the step (untouched until phases 2 / 3 of the next one) and its a1o buffer.
-    auto update_w1_w2 = [&](const double *a1o) {
+    // ---- the W1 / W2 updates of a step (phase 5b) are deferred into the barrier waits of the NEXT step, where every CTA
+    // idles anyway: the own-column copy of W1 (first needed by phase 2) under barrier 1, the own-row copy of W1 and W2
+    // (first needed by phases 3 / 4) under barrier 2; after the loop for the last step.  Inputs: dl2, a1, dl3, a2 of the
+    // step (untouched until phases 2 / 3 of the next one) and its a1o buffer.
+    auto update_w1_columns = [&]() {
         // W1[:, own columns] (forward copy): g = sum_b delta2[b][k] * a1[b][j]
         for (int kk = 0; kk < nc1; kk++)
             for (int j = tid; j < d1; j += NT) {
@@ -292,6 +293,8 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
                 w1c[kk * d1 + j] = __dsub_rn(w1c[kk * d1 + j], adj);
                 *vp = adj;
             }
+    };
+    auto update_w1_rows_w2 = [&](const double *a1o) {
         // W1[own rows, :] (backprop copy): same arithmetic on the same inputs => identical values
         for (int e = tid; e < nc0 * d2; e += NT) {  // all (row, column) pairs at once: one L2 round trip, not nc0
             const int jj = e / d2, k = e - jj * d2;
@@ -391,7 +394,7 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         // thread 0 waits for the other CTAs
         grid_barrier_overlap(p.bar, bar_target, gave_up, [&] {
             if (p.bulk && u8 && warp == 1 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, stage, mbar, lane);
-            if (it > 0) update_w1_w2(a1o_buf + (size_t)((it - 1) & 1) * B * ncm);   // phase 5b of the previous step
+            if (it > 0) update_w1_columns();   // phase 5b of the previous step, first part
         });
         K1_MARK(2)  // barrier 1
 
@@ -423,7 +426,9 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
         }
         K1_MARK(3)  // phase 2
         bar_target += G;
-        grid_barrier(p.bar, bar_target, gave_up);
+        grid_barrier_overlap(p.bar, bar_target, gave_up, [&] {
+            if (it > 0) update_w1_rows_w2(a1o_buf + (size_t)((it - 1) & 1) * B * ncm);   // ... second part
+        });
         K1_MARK(4)  // barrier 2
 
         // ---- phase 3 (replicated): a2 = f(z2), z3 = a2 . W2, output delta, delta2 ----
@@ -591,13 +596,14 @@ __global__ void __launch_bounds__(512, 1) fused_train_kernel(const FusedParams p
             __syncthreads();
             if (warp == 0 && it + 1 < p.iters) issue_batch_fetch(p, it + 1, a0, mbar, lane);
         }
-        // (phase 5b, the W1 / W2 updates, runs under barrier 1 of the next step: see update_w1_w2)
+        // (phase 5b, the W1 / W2 updates, runs under the barrier waits of the next step: see update_w1_columns)
         __syncthreads();
         K1_MARK(7)  // phase 5
     }
 
     if (p.iters > 0) {
-        update_w1_w2(a1o_buf + (size_t)((p.iters - 1) & 1) * B * ncm);
+        update_w1_columns();
+        update_w1_rows_w2(a1o_buf + (size_t)((p.iters - 1) & 1) * B * ncm);
         __syncthreads();
     }
     if (p.prof != nullptr && c == 0 && tid == 0)
