@@ -8,7 +8,7 @@
 // tcgen05.mma.cta_group::2): a pair owns a 256 x 256 output tile, each CTA stages ITS 128 rows of A and
 // ITS 128 rows of B per 64-deep K block, the leader's single MMA thread drives both tensor cores, and each
 // CTA's TMEM receives its 128 accumulator rows.
-//   warp 0      TMA producer   : cp.async.bulk.tensor, 64x64 128B-swizzled boxes, 6-stage 32 KB ring
+//   warp 0      TMA producer   : cp.async.bulk.tensor, 64x64 128B-swizzled boxes, 5-stage 32 KB ring
 //   warp 1      MMA issuer     : leader CTA only; M=256, N=256 (or 128), K=16 per instruction
 //   warps 2..9  epilogue       : tcgen05.ld 32x32b -> registers -> fused epilogue -> global (row-major)
 // Pipelines: smem full/empty ring and a double-buffered TMEM accumulator (2 x 256 columns) so the epilogue
@@ -46,7 +46,12 @@ namespace b2nn {
 constexpr int GEMM_BM = 128;        // rows of A per CTA (pair tile: 256)
 constexpr int GEMM_BN = 256;        // pair tile width
 constexpr int GEMM_BK = 64;         // 64 bf16 = 128 B = one swizzle row (BF16 operands; GemmCfg<true> for TF32)
-constexpr int GEMM_STAGES = 6;
+#ifndef B2NN_GEMM_STAGES
+#define B2NN_GEMM_STAGES 5
+#endif
+constexpr int GEMM_STAGES = B2NN_GEMM_STAGES;   // 5 x 32 KB operand stages + 32 KB of epilogue staging (fused-update epilogue) =
+                                                // the 198 KB footprint of the 6-stage kernel of round 1: the kernels that run
+                                                // beside the GEMM CTA (input prologue, exchange) still find shared memory on the SM
 #ifndef B2NN_GEMM_EPI_WARPS
 #define B2NN_GEMM_EPI_WARPS 8
 #endif
@@ -59,7 +64,11 @@ constexpr int GEMM_CHUNK_BYTES = 64 * GEMM_BK * 2;      // one 64 x 64 TMA box: 
 constexpr int GEMM_A_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of A
 constexpr int GEMM_B_BYTES = 2 * GEMM_CHUNK_BYTES;      // this CTA's 128 rows of B (64 for a half tile)
 constexpr int GEMM_STAGE_BYTES = GEMM_A_BYTES + GEMM_B_BYTES;
-constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers, item ring*/;
+// staging of the fused-update epilogue: 4 KB per epilogue warp (a 32-row x 32-column FP32 accumulator chunk)
+constexpr int GEMM_EPI_STAGE_BYTES = 32 * 128;
+constexpr int GEMM_SMEM_BYTES = GEMM_STAGES * GEMM_STAGE_BYTES + 1024 /*align*/ + 512 /*barriers, item ring*/ +
+                                GEMM_EPI_WARPS * GEMM_EPI_STAGE_BYTES;
+static_assert(GEMM_SMEM_BYTES + 1024 <= 232448, "shared memory of one CTA (227 KB incl. the 1 KB the system reserves)");
 constexpr uint32_t GEMM_TMEM_COLS = 512;  // 2 accumulators x 256 fp32 columns
 constexpr int GEMM_SCHED_SLOTS = 4;       // depth of the work-item ring between the scheduler and the role warps
 constexpr int GEMM_SCHED_READERS = 2 /*producers*/ + 1 /*MMA*/ + 2 * GEMM_EPI_WARPS;
@@ -82,7 +91,7 @@ enum EpiKind {
     EPI_ACT = 0,        // a = f(acc): store out0[M][ld0] in the operand type (BF16, or FP32 for TF32 nets)
     EPI_LOGITS = 1,     // store FP32 acc to out0[M][ld0]
     EPI_DX = 2,         // d = acc * f'(from stored activation aux[M][ldaux]): store out0 in the operand type
-    EPI_DW_UPDATE = 3,  // v = s*acc + mu*v; w -= v (FP32 master w,v [M][ldw]); BF16 copy of w to out0
+    EPI_DW_UPDATE = 3,  // v = s*acc + mu*v; w -= v (FP32 master w,v [M][ldw]); BF16 copy of w to out0 (BF16 nets)
     EPI_DW_STORE = 4,   // store FP32 acc (the summed gradient) to w[M][ldw]
     EPI_DW_STORE_BF16 = 5  // store the summed gradient rounded to BF16 to out0[M][ld0] (B2NN_FLAG_BF16_WIRE)
 };
@@ -279,39 +288,6 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
         default: dx32(u, r, x, [](float) { return 1.f; });
         }
         store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
-    } else if constexpr (EPI == EPI_DW_UPDATE) {
-        static_assert(!TF32, "the fused-update epilogue emits the BF16 operand copy; TF32 nets have none");
-        // momentum SGD fused into the gradient GEMM (SoftmaxCrossEntropyNeuralNet.java:325-342):
-        // adj = step*G/B + mu*prev ; W -= adj ; prev = adj.  G never reaches HBM.
-        float *wrow = g.w + (size_t)m * g.ldw + n0;
-        float *vrow = g.v + (size_t)m * g.ldw + n0;
-        float x[32];
-        if (n0 + 32 <= g.N) {
-#pragma unroll
-            for (int q = 0; q < 8; q++) {
-                float4 w4 = reinterpret_cast<const float4 *>(wrow)[q];
-                float4 v4 = reinterpret_cast<const float4 *>(vrow)[q];
-                v4.x = g.scale * __uint_as_float(r[4 * q + 0]) + g.momentum * v4.x;
-                v4.y = g.scale * __uint_as_float(r[4 * q + 1]) + g.momentum * v4.y;
-                v4.z = g.scale * __uint_as_float(r[4 * q + 2]) + g.momentum * v4.z;
-                v4.w = g.scale * __uint_as_float(r[4 * q + 3]) + g.momentum * v4.w;
-                w4.x -= v4.x; w4.y -= v4.y; w4.z -= v4.z; w4.w -= v4.w;
-                reinterpret_cast<float4 *>(wrow)[q] = w4;
-                reinterpret_cast<float4 *>(vrow)[q] = v4;
-                x[4 * q + 0] = w4.x; x[4 * q + 1] = w4.y; x[4 * q + 2] = w4.z; x[4 * q + 3] = w4.w;
-            }
-        } else {
-#pragma unroll
-            for (int c = 0; c < 32; c++) {
-                x[c] = 0.f;
-                if (n0 + c < g.N) {
-                    float vn = g.scale * __uint_as_float(r[c]) + g.momentum * vrow[c];
-                    float wn = wrow[c] - vn;
-                    vrow[c] = vn; wrow[c] = wn; x[c] = wn;
-                }
-            }
-        }
-        store_bf16_row(reinterpret_cast<__nv_bfloat16 *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_DW_STORE_BF16) {
         float x[32];
 #pragma unroll
@@ -320,6 +296,57 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
     } else {  // EPI_DW_STORE
         store_f32_row(g.w, g.ldw, g.N, m, n0, r);
     }
+}
+
+// ---- EPI_DW_UPDATE: momentum SGD fused into the gradient GEMM (SoftmaxCrossEntropyNeuralNet.java:325-342) ----------
+// adj = step*G/B + mu*prev ; W -= adj ; prev = adj, on the FP32 master arrays, plus the BF16 operand copy (BF16 nets).  The
+// summed gradient never reaches HBM and there is no separate update kernel streaming 22 B per parameter through the
+// SMs' memory ports beside the contractions (13 % of the C4 step, profiles/r02_notes.md).
+// The accumulator arrives one ROW per thread (tcgen05.ld 32x32b: lane = row); read-modify-write of w and v in that shape
+// is 32 scattered 16-byte requests per warp instruction (round 1: 3.4 ms/step).  So the warp parks its 32 x 32 chunk in
+// shared memory (16-byte slots XOR-swizzled by row: conflict-free both ways) and takes it back with EIGHT LANES PER ROW:
+// every warp-wide load / store of w, v and the operand copy then covers four whole 128-byte row segments.
+template <bool TF32>
+__device__ __forceinline__ void epilogue_update_quad(const GemmArgs &g, int m, int n, float4 acc) {
+    if (m >= g.M || n >= g.N) return;
+    float *wp = g.w + (size_t)m * g.ldw + n, *vp = g.v + (size_t)m * g.ldw + n;
+    float x[4];
+    if (n + 4 <= g.N) {
+        float4 w4 = *reinterpret_cast<const float4 *>(wp), v4 = *reinterpret_cast<const float4 *>(vp);
+        v4.x = g.scale * acc.x + g.momentum * v4.x; v4.y = g.scale * acc.y + g.momentum * v4.y;
+        v4.z = g.scale * acc.z + g.momentum * v4.z; v4.w = g.scale * acc.w + g.momentum * v4.w;
+        w4.x -= v4.x; w4.y -= v4.y; w4.z -= v4.z; w4.w -= v4.w;
+        *reinterpret_cast<float4 *>(wp) = w4;
+        *reinterpret_cast<float4 *>(vp) = v4;
+        if constexpr (!TF32)   // TF32 nets: the FP32 master array IS the GEMM operand
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(g.out0) + (size_t)m * g.ld0 + n) =
+                make_uint2(pack_bf16x2(w4.x, w4.y), pack_bf16x2(w4.z, w4.w));
+    } else {
+        const float a[4] = {acc.x, acc.y, acc.z, acc.w};
+        for (int c = 0; n + c < g.N; c++) {
+            const float vn = g.scale * a[c] + g.momentum * vp[c];
+            x[c] = wp[c] - vn;
+            vp[c] = vn; wp[c] = x[c];
+            if constexpr (!TF32) reinterpret_cast<__nv_bfloat16 *>(g.out0)[(size_t)m * g.ld0 + n + c] = __float2bfloat16_rn(x[c]);
+        }
+    }
+}
+// one 32-row x 32-column accumulator chunk of this warp: r = row `lane`; m_base / n_base = its first row / column
+template <bool TF32>
+__device__ __forceinline__ void epilogue_update_chunk(const GemmArgs &g, float4 *stage, int lane, int m_base, int n_base,
+                                                      const uint32_t (&r)[32]) {
+#pragma unroll
+    for (int q = 0; q < 8; q++)
+        stage[lane * 8 + (q ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                                          __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+    __syncwarp();
+    const int slot = lane & 7;
+#pragma unroll 4
+    for (int i = 0; i < 8; i++) {
+        const int row = 4 * i + (lane >> 3);
+        epilogue_update_quad<TF32>(g, m_base + row, n_base + 4 * slot, stage[row * 8 + (slot ^ (row & 7))]);
+    }
+    __syncwarp();  // the chunk is out before the next one overwrites the staging rows
 }
 
 // Work list of one launch: items [0, full) are 256 x 256 tiles in row-major tile order, items
@@ -392,6 +419,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     ring.sempty = ring.sfull + GEMM_SCHED_SLOTS;
     ring.sitem = reinterpret_cast<volatile uint32_t *>(ring.sempty + GEMM_SCHED_SLOTS);
     ring.sempty_rank1 = ptx::map_to_rank(ring.sempty, 1);
+    float4 *epi_stage_base = reinterpret_cast<float4 *>(smem + GEMM_STAGES * GEMM_STAGE_BYTES + 512);
     if (g.tile_counter == nullptr) { ring.static_next = (int)(blockIdx.x >> 1); ring.static_stride = (int)(gridDim.x >> 1); }
 
     const int warp = threadIdx.x >> 5;
@@ -566,7 +594,11 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
                 uint32_t r[32];
                 ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
                 ptx::tmem_ld_wait();
-                epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r);
+                if constexpr (EPI == EPI_DW_UPDATE)
+                    epilogue_update_chunk<TF32>(g, epi_stage_base + (size_t)(warp - 2) * (GEMM_EPI_STAGE_BYTES / 16), lane,
+                                                m0 + rank * GEMM_BM + q * 32, n0 + c0, r);
+                else
+                    epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r);
             }
             ptx::tc_fence_before();
             __syncwarp();

@@ -189,7 +189,7 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
 
 template <int EPI, bool A_MN, bool B_MN>
 static int launch_gemm(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap &tb, const GemmArgs &g) {
-    if constexpr (EPI != EPI_DW_UPDATE && EPI != EPI_DW_STORE_BF16) {
+    if constexpr (EPI != EPI_DW_STORE_BF16) {
         if (is_tf32(net)) return launch_gemm_t<EPI, A_MN, B_MN, true>(net, ta, tb, g);
     }
     return launch_gemm_t<EPI, A_MN, B_MN, false>(net, ta, tb, g);
@@ -595,9 +595,10 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
     GemmArgs g{};
     g.M = y.in; g.N = y.out; g.K = B;
     g.ldw = y.ld_n;
-    if (net->world == 1 && net->fused_update && !is_tf32(net)) {
+    if (net->world == 1 && net->fused_update) {
+        // single GPU: the momentum update rides in the gradient GEMM's epilogue (no gradient array, no update kernel)
         g.w = y.w; g.v = y.v;
-        g.out0 = y.wn; g.ld0 = y.ld_n;
+        g.out0 = y.wn; g.ld0 = y.ld_n;   // BF16 operand copy (null for TF32 nets: w itself is the operand)
         g.scale = scale; g.momentum = momentum;
         return launch_gemm<EPI_DW_UPDATE, true, true>(net, b.tm_a_mn[l], b.tm_d_mn[l + 1], g);
     }
@@ -702,7 +703,7 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
     const float mu = (float)momentum;
     // with b2nn_profile_enable on, everything runs in stream order so that the event pairs time each contraction alone
     const bool side = (net->world > 1 || net->overlap_update) && !net->profiling;
-    if (net->backward_reorder && !(net->fused_update && !is_tf32(net))) {
+    if (net->backward_reorder && !(net->fused_update && net->world == 1)) {
         for (int l = L - 1; l >= 1; l--) B2_TRY(launch_delta(net, l, B));
         for (int l = 0; l < L; l++)
             B2_TRY(launch_gradient_and_update(net, l, B, scale, mu, side ? net->aux_stream : net->stream));
