@@ -306,32 +306,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
 // is 32 scattered 16-byte requests per warp instruction (round 1: 3.4 ms/step).  So the warp parks its 32 x 32 chunk in
 // shared memory (16-byte slots XOR-swizzled by row: conflict-free both ways) and takes it back with EIGHT LANES PER ROW:
 // every warp-wide load / store of w, v and the operand copy then covers four whole 128-byte row segments.
-template <bool TF32>
-__device__ __forceinline__ void epilogue_update_quad(const GemmArgs &g, int m, int n, float4 acc) {
-    if (m >= g.M || n >= g.N) return;
-    float *wp = g.w + (size_t)m * g.ldw + n, *vp = g.v + (size_t)m * g.ldw + n;
-    float x[4];
-    if (n + 4 <= g.N) {
-        float4 w4 = *reinterpret_cast<const float4 *>(wp), v4 = *reinterpret_cast<const float4 *>(vp);
-        v4.x = g.scale * acc.x + g.momentum * v4.x; v4.y = g.scale * acc.y + g.momentum * v4.y;
-        v4.z = g.scale * acc.z + g.momentum * v4.z; v4.w = g.scale * acc.w + g.momentum * v4.w;
-        w4.x -= v4.x; w4.y -= v4.y; w4.z -= v4.z; w4.w -= v4.w;
-        *reinterpret_cast<float4 *>(wp) = w4;
-        *reinterpret_cast<float4 *>(vp) = v4;
-        if constexpr (!TF32)   // TF32 nets: the FP32 master array IS the GEMM operand
-            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(g.out0) + (size_t)m * g.ld0 + n) =
-                make_uint2(pack_bf16x2(w4.x, w4.y), pack_bf16x2(w4.z, w4.w));
-    } else {
-        const float a[4] = {acc.x, acc.y, acc.z, acc.w};
-        for (int c = 0; n + c < g.N; c++) {
-            const float vn = g.scale * a[c] + g.momentum * vp[c];
-            x[c] = wp[c] - vn;
-            vp[c] = vn; wp[c] = x[c];
-            if constexpr (!TF32) reinterpret_cast<__nv_bfloat16 *>(g.out0)[(size_t)m * g.ld0 + n + c] = __float2bfloat16_rn(x[c]);
-        }
-    }
-}
-// one 32-row x 32-column accumulator chunk of this warp: r = row `lane`; m_base / n_base = its first row / column
+// one 32-row x 32-column accumulator chunk of this warp: r = row `lane`; m_base / n_base = its first row / column.
+// Phase 1 issues ALL of the chunk's w / v loads (16 x 16 bytes per lane in flight: one memory round trip per chunk --
+// interleaved with the stores the compiler must keep them in order, w and v being written through the same pointers);
+// phase 2 takes the accumulators back from the staging rows, updates and stores.
 template <bool TF32>
 __device__ __forceinline__ void epilogue_update_chunk(const GemmArgs &g, float4 *stage, int lane, int m_base, int n_base,
                                                       const uint32_t (&r)[32]) {
@@ -340,13 +318,63 @@ __device__ __forceinline__ void epilogue_update_chunk(const GemmArgs &g, float4 
         stage[lane * 8 + (q ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
                                                           __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
     __syncwarp();
-    const int slot = lane & 7;
-#pragma unroll 4
+    const int slot = lane & 7, n = n_base + 4 * slot;
+    const int row0 = lane >> 3;                       // this lane's rows: row0 + 4 i
+    const bool col_ok = n < g.N, full = n + 4 <= g.N;
+    float4 w4[8], v4[8];
+#pragma unroll
     for (int i = 0; i < 8; i++) {
-        const int row = 4 * i + (lane >> 3);
-        epilogue_update_quad<TF32>(g, m_base + row, n_base + 4 * slot, stage[row * 8 + (slot ^ (row & 7))]);
+        const int m = m_base + row0 + 4 * i;
+        w4[i] = v4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (col_ok && m < g.M) {
+            const float *wp = g.w + (size_t)m * g.ldw + n, *vp = g.v + (size_t)m * g.ldw + n;
+            if (full) {
+                w4[i] = *reinterpret_cast<const float4 *>(wp);
+                v4[i] = *reinterpret_cast<const float4 *>(vp);
+            } else {   // ragged right edge: up to three valid columns
+                w4[i].x = wp[0]; v4[i].x = vp[0];
+                if (n + 1 < g.N) { w4[i].y = wp[1]; v4[i].y = vp[1]; }
+                if (n + 2 < g.N) { w4[i].z = wp[2]; v4[i].z = vp[2]; }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int row = row0 + 4 * i, m = m_base + row;
+        if (!col_ok || m >= g.M) continue;
+        const float4 acc = stage[row * 8 + (slot ^ (row & 7))];
+        float4 V = v4[i], W = w4[i];
+        V.x = g.scale * acc.x + g.momentum * V.x; V.y = g.scale * acc.y + g.momentum * V.y;
+        V.z = g.scale * acc.z + g.momentum * V.z; V.w = g.scale * acc.w + g.momentum * V.w;
+        W.x -= V.x; W.y -= V.y; W.z -= V.z; W.w -= V.w;
+        float *wp = g.w + (size_t)m * g.ldw + n, *vp = g.v + (size_t)m * g.ldw + n;
+        if (full) {
+            *reinterpret_cast<float4 *>(wp) = W;
+            *reinterpret_cast<float4 *>(vp) = V;
+            if constexpr (!TF32)   // TF32 nets: the FP32 master array IS the GEMM operand
+                *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(g.out0) + (size_t)m * g.ld0 + n) =
+                    make_uint2(pack_bf16x2(W.x, W.y), pack_bf16x2(W.z, W.w));
+        } else {
+            const float wv[3] = {W.x, W.y, W.z}, vv[3] = {V.x, V.y, V.z};
+            for (int c = 0; n + c < g.N; c++) {
+                wp[c] = wv[c]; vp[c] = vv[c];
+                if constexpr (!TF32) reinterpret_cast<__nv_bfloat16 *>(g.out0)[(size_t)m * g.ld0 + n + c] = __float2bfloat16_rn(wv[c]);
+            }
+        }
     }
     __syncwarp();  // the chunk is out before the next one overwrites the staging rows
+}
+// pull the w / v lines a warp will update (32 rows x `cols` columns from (m_base, n_base)) into L2 while the tile's main
+// loop is still running: the read-modify-write then starts from L2 hits instead of DRAM round trips
+__device__ __forceinline__ void epilogue_update_prefetch(const GemmArgs &g, int lane, int m_base, int n_base, int cols) {
+    const int lines = (cols * 4 + 127) / 128;         // 128-byte lines per row and array
+    for (int e = lane; e < 32 * lines; e += 32) {
+        const int m = m_base + e / lines, n = n_base + (e % lines) * 32;
+        if (m < g.M && n < g.N) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(g.w + (size_t)m * g.ldw + n));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(g.v + (size_t)m * g.ldw + n));
+        }
+    }
 }
 
 // Work list of one launch: items [0, full) are 256 x 256 tiles in row-major tile order, items
@@ -582,6 +610,9 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
         for (int item = ring.next(true, lane); item < sched.total; item = ring.next(true, lane)) {
             int m0, n0, bn;
             sched.decode(item, m0, n0, bn);
+            if constexpr (EPI == EPI_DW_UPDATE)   // while the tile's main loop runs
+                epilogue_update_prefetch(g, lane, m0 + rank * GEMM_BM + q * 32, n0 + part * (bn / GEMM_EPI_PARTS),
+                                         bn / GEMM_EPI_PARTS);
             const uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             const uint32_t c1 = g.stalls ? (uint32_t)clock64() : 0u;
