@@ -147,7 +147,8 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16", extra_flags=0
     torch.cuda.set_device(rank)
     dist = _init(rank, world, port, "nccl")
     g = ge.load_package()
-    dims, gB, iters, step, mu = [256, 384, 128, 40], 256 * world, 6, 0.05, 0.9
+    rows_per_rank = int(os.environ.get("B2NN_TEST_ROWS_PER_RANK", "256"))
+    dims, gB, iters, step, mu = [256, 384, 128, 40], rows_per_rank * world, 6, 0.05, 0.9
     prec = g.capi.PREC_TF32 if precision_name == "tf32" else g.capi.PREC_BF16
     flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX | extra_flags
     rng = np.random.RandomState(11)
@@ -175,7 +176,11 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16", extra_flags=0
         w0 = single.getWeights()
         for it in range(iters):
             single.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu)
-        np.savez(os.path.join(out_dir, "nccl.npz"), w_dp=w, w_single=single.getWeights(), w0=w0,
+        w_single = single.getWeights()
+        sys.stderr.write("[dp worker] world %d %s %s: |dW_dp| %.4g |dW_single| %.4g finite %s %s\n" % (
+            world, precision_name, net.commMode(), np.linalg.norm(w - w0), np.linalg.norm(w_single - w0),
+            np.isfinite(w).all(), np.isfinite(w_single).all()))
+        np.savez(os.path.join(out_dir, "nccl.npz"), w_dp=w, w_single=w_single, w0=w0,
                  replicas_equal=int(flag.item()), launches=net.kernelLaunches(), mode=net.commMode())
     dist.barrier()
     dist.destroy_process_group()
