@@ -94,8 +94,8 @@ enum b2nn_flags {
     /* data-parallel BF16 nets only: the per-GPU batch gradients travel as BF16 instead of FP32 (the gradient GEMM's
      * epilogue stores BF16, the fused exchange kernel reads 2 B per parameter and peer instead of 4 and sums in FP32).
      * Halves the exchange's wire and memory traffic; costs one BF16 rounding of every per-GPU gradient (and, with the
-     * in-switch reduction, of their sum): ~3e-3 relative on the update, above the 2e-3 bound the FP32 exchange is held
-     * to -- so it is opt-in, never the default.  Ignored by single-GPU nets and by the NCCL exchange. */
+     * in-switch reduction, of their sum): 2e-3 .. 8e-3 relative on the update over a few steps against 1e-6 .. 7e-4 for the
+     * FP32 exchange -- so it is opt-in, never the default.  Ignored by single-GPU nets and by the NCCL exchange. */
     B2NN_FLAG_BF16_WIRE = 4
 };
 

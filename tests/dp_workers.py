@@ -177,6 +177,13 @@ def nccl_worker(rank, world, port, out_dir, precision_name="bf16", extra_flags=0
         for it in range(iters):
             single.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu)
         w_single = single.getWeights()
+        if os.environ.get("B2NN_TEST_DIAG"):   # a second comparator, stepped with the per-step loss read back
+            again = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=prec,
+                                                   flags=flags & ~g.capi.FLAG_BF16_WIRE, device=0)
+            ls = [again.gradientStepLabeled(x[idx[it]], lab[idx[it]], step, mu, returnLoss=True) for it in range(iters)]
+            sys.stderr.write("[dp worker] second comparator: losses %s |dW| %.4g launches %d / %d\n" % (
+                ["%.4f" % l for l in ls], np.linalg.norm(again.getWeights() - w0), single.kernelLaunches(),
+                again.kernelLaunches()))
         sys.stderr.write("[dp worker] world %d %s %s: |dW_dp| %.4g |dW_single| %.4g finite %s %s\n" % (
             world, precision_name, net.commMode(), np.linalg.norm(w - w0), np.linalg.norm(w_single - w0),
             np.isfinite(w).all(), np.isfinite(w_single).all()))
