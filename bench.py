@@ -442,6 +442,21 @@ def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, wan
                               "gathered over PCIe from pinned host memory by the input prologue kernel on a copy stream "
                               "(double-buffered under the previous step's GEMMs); per-step loss read back"}
         ds_e2e.close()
+        if e2e_rows != "u8" and not tf32 and name == "c4":
+            # the same leg with the rows in the reference's own storage format -- IDX pixel bytes, read as
+            # (raw & 0xff) / 255.0 (MNISTTrainer.java:97) -- i.e. half the bytes over PCIe; reported beside the BF16 leg
+            x8 = np.minimum(np.floor(x * 256.0), 255.0).astype(np.uint8)
+            ds8 = g.Dataset(net, x8, labels=labels, location=g.capi.DATA_HOST_PINNED)
+            train_call(g, net, ds8, idx_warm[:min(3, idx_warm.shape[0])], B, step, want_loss=True)
+            ctx.barrier()
+            t0 = time.perf_counter()
+            train_call(g, net, ds8, idx_time, B, step, want_loss=True)
+            torch.cuda.synchronize()
+            s8 = ctx.max_over_ranks(time.perf_counter() - t0)
+            ctx.barrier()
+            res["e2e"]["pixel_byte_rows"] = {"value": gB * K / s8, "unit": "samples/s", "ms_per_step": s8 / K * 1e3,
+                                             "h2d_bytes_per_step": B * dims[0] + B * 4}
+            ds8.close()
 
     # ---- sustained leg (last: it heats the part up): the same call back to back for >= 2 s, power-capped clocks ------
     if want_sustained:

@@ -335,3 +335,32 @@ def test_host_pinned_dataset_matches_device(g):
         g.capi.check(g.capi.lib().b2nn_train_indexed(net._h, ds._h, idx.ctypes.data_as(C.POINTER(C.c_int32)), 6, B,
                                                      0.05, 0.9, None))
     assert np.array_equal(a.getWeights(), b.getWeights())
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+@pytest.mark.parametrize("dims,B", [([512, 384, 256, 100], 256), ([300, 131, 70, 10], 96)])
+def test_fused_update_epilogue_matches_separate_update_kernel(g, prec, dims, B, monkeypatch):
+    """single GPU: the momentum update rides in the gradient GEMM's epilogue (EPI_DW_UPDATE: accumulator chunk staged
+    through shared memory, coalesced read-modify-write of w / v, S:325-342) by default; B2NN_FUSED_UPDATE=0 stores the
+    summed gradient and runs the separate update kernel.  Same FP32 operations on the same accumulators: weights and
+    velocity agree to FP32 rounding of one multiply-add (<= 1e-6 of the update, the compiler may contract differently)
+    over 4 momentum steps; dims with widths that are no multiple of 4 exercise the ragged right edge of a quad."""
+    precision = g.capi.PREC_BF16 if prec == "bf16" else g.capi.PREC_TF32
+    flags = g.capi.FLAG_SCALED_INIT | g.capi.FLAG_STABLE_SOFTMAX
+    rng = np.random.RandomState(17)
+    x = rng.rand(B, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], B).astype(np.int32)
+    out = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("B2NN_FUSED_UPDATE", fused)
+        net = g.SoftmaxCrossEntropyNeuralNet(dims, g.LEAKY_RELU, g.LEAKY_RELU_PRIME, precision=precision, flags=flags)
+        w0 = net.getWeights()
+        k0 = net.kernelLaunches()
+        for _ in range(4):
+            net.gradientStepLabeled(x, lab, 0.05, 0.9)
+        out.append((net.getWeights() - w0, net.getVelocity(), net.kernelLaunches() - k0))
+        net.close()
+    (du_f, v_f, k_f), (du_s, v_s, k_s) = out
+    assert k_f == k_s - 4 * (len(dims) - 1)                 # one update kernel per layer and step fewer
+    assert np.linalg.norm(du_f - du_s) <= 1e-6 * np.linalg.norm(du_s)
+    assert np.linalg.norm(v_f - v_s) <= 1e-6 * np.linalg.norm(v_s)
