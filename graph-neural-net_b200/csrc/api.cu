@@ -218,6 +218,7 @@ int b2nn_profile_enable(b2nn_net *net, int32_t on) {
     }
     B2_TRY(profile_flush(net));
     net->profiling = on != 0;
+    net->prof_grouped = on == 2;   // one event pair per run of consecutive contraction launches instead of one per launch
     net->prof_flops = 0; net->prof_ms_acc = 0; net->prof_launch_acc = 0;
     for (int c = 0; c < 4; c++) { net->prof_ms_cls[c] = 0; net->prof_n_cls[c] = 0; }
     return B2NN_OK;

@@ -214,6 +214,9 @@ struct b2nn_net {
     // profiling (b2nn_profile_enable): event pairs around the launches of the tensor-core path, by kernel class
     // (0 contraction, 1 momentum update / exchange, 2 output delta, 3 input prologue + label gather)
     bool profiling = false;
+    bool prof_grouped = false;      // b2nn_profile_enable(net, 2): ONE pair around each run of consecutive contraction launches
+    cudaEvent_t prof_pending = nullptr;       // stop event of the open contraction window (grouped mode), not yet recorded
+    cudaStream_t prof_pending_stream = nullptr;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     std::vector<unsigned char> prof_cls;   // class of pair i (events 2i, 2i+1)
     size_t prof_used = 0;

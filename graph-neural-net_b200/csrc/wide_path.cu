@@ -89,8 +89,18 @@ void trace_dump(b2nn_net *net, int first, int count) {
     net->trace_marks.clear();
 }
 
+// grouped mode: record the stop event of the open contraction window
+static int prof_close(b2nn_net *net) {
+    if (net->prof_pending) {
+        B2_CHECK_CUDA(cudaEventRecord(net->prof_pending, net->prof_pending_stream));
+        net->prof_pending = nullptr;
+    }
+    return B2NN_OK;
+}
+
 // fold the recorded event pairs into the accumulators (synchronises the stream)
 int profile_flush(b2nn_net *net) {
+    B2_TRY(prof_close(net));
     if (net->prof_used) {
         B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
         if (net->copy_stream) B2_CHECK_CUDA(cudaStreamSynchronize(net->copy_stream));
@@ -100,18 +110,31 @@ int profile_flush(b2nn_net *net) {
             const int cls = net->prof_cls[i / 2] & 3;
             net->prof_ms_cls[cls] += ms;
             net->prof_n_cls[cls]++;
-            if (cls == 0) { net->prof_ms_acc += ms; net->prof_launch_acc++; }
+            if (cls == 0) net->prof_ms_acc += ms;   // launches of class 0 are counted where they are made
         }
         net->prof_used = 0;
     }
     return B2NN_OK;
 }
 
-// event pair of class `cls` around whatever is launched on `st` between prof_begin and prof_end (profiling on only)
-struct ProfPair { cudaEvent_t e1 = nullptr; };
+// event pair of class `cls` around whatever is launched on `st` between prof_begin and prof_end (profiling on only).
+// A timing event between two kernels costs the stream several microseconds of idle time, part of which lands INSIDE the
+// next window (profiles/r02_notes.md: 8 windows per C4 step summed to more than the whole overlapped step).  In grouped
+// mode consecutive contraction launches on one stream therefore share ONE window: its stop event stays pending until
+// something else is about to be launched (another class, another stream, the end of the forward / backward pass).
+struct ProfPair { cudaEvent_t e1 = nullptr; int cls = 0; };
 static int prof_begin(b2nn_net *net, int cls, cudaStream_t st, ProfPair *pp) {
     pp->e1 = nullptr;
+    pp->cls = cls;
     if (!net->profiling) return B2NN_OK;
+    if (net->prof_pending) {
+        if (cls == 0 && st == net->prof_pending_stream) {   // the open window goes on
+            pp->e1 = net->prof_pending;
+            net->prof_pending = nullptr;
+            return B2NN_OK;
+        }
+        B2_TRY(prof_close(net));
+    }
     if (net->prof_used + 2 > net->prof_events.size()) B2_TRY(profile_flush(net));
     net->prof_cls[net->prof_used / 2] = (unsigned char)cls;
     cudaEvent_t e0 = net->prof_events[net->prof_used++];
@@ -119,8 +142,10 @@ static int prof_begin(b2nn_net *net, int cls, cudaStream_t st, ProfPair *pp) {
     B2_CHECK_CUDA(cudaEventRecord(e0, st));
     return B2NN_OK;
 }
-static int prof_end(cudaStream_t st, const ProfPair &pp) {
-    if (pp.e1) B2_CHECK_CUDA(cudaEventRecord(pp.e1, st));
+static int prof_end(b2nn_net *net, cudaStream_t st, const ProfPair &pp) {
+    if (!pp.e1) return B2NN_OK;
+    if (net->prof_grouped && pp.cls == 0) { net->prof_pending = pp.e1; net->prof_pending_stream = st; return B2NN_OK; }
+    B2_CHECK_CUDA(cudaEventRecord(pp.e1, st));
     return B2NN_OK;
 }
 
@@ -180,8 +205,8 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
                     EPI, g.M, g.N, g.K, s[3] / P, s[4] / P, s[1] / P, s[2] / P, s[0] / C, s[5] / C, s[6] / C,
                     s[6] / C / (s[4] / P));
     }
-    B2_TRY(prof_end(net->stream, pp));
-    if (net->profiling) net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
+    B2_TRY(prof_end(net, net->stream, pp));
+    if (net->profiling) { net->prof_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K; net->prof_launch_acc++; }
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -204,7 +229,7 @@ static int launch_update(b2nn_net *net, WideLayer &y, float scale, float momentu
     B2_TRY(prof_begin(net, 1, st, &pp));
     wide::sgd_update<<<(int)blocks, 256, 0, st>>>((const float4 *)y.g, (float4 *)y.w, (float4 *)y.v, n4, scale,
                                                   momentum, cast_only, (uint2 *)y.wn);
-    B2_TRY(prof_end(st, pp));
+    B2_TRY(prof_end(net, st, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -517,7 +542,7 @@ int wide_prologue(b2nn_net *net, const void *X, int x_dtype, const int32_t *idx_
     default: B2_REQUIRE(false, B2NN_ERR_INVALID_ARG, "unknown x dtype %d", x_dtype);
     }
     }
-    B2_TRY(prof_end(st, pp));
+    B2_TRY(prof_end(net, st, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -545,7 +570,7 @@ int wide_forward(b2nn_net *net, int B) {
         }
         trace_mark(net, net->stream, "fwd", l);
     }
-    return B2NN_OK;
+    return prof_close(net);   // whatever follows on this stream is not a contraction
 }
 
 // K5/K6: output delta + per-row loss
@@ -564,7 +589,7 @@ int wide_output(b2nn_net *net, int B, bool dense_targets, double *loss_slot_dev)
             b.logits, ldL, dense_targets ? nullptr : b.labels, dense_targets ? b.tdense : nullptr, ldL, B, dL, net->kind,
             net->last_act, (float)net->last_param, (__nv_bfloat16 *)b.d[L], ldL, b.row_loss, loss_slot_dev,
             b.block_partial, b.block_counter);
-    B2_TRY(prof_end(net->stream, pp));
+    B2_TRY(prof_end(net, net->stream, pp));
     net->launches++;
     B2_CHECK_CUDA(cudaGetLastError());
     return B2NN_OK;
@@ -639,7 +664,7 @@ static int launch_gradient_and_update(b2nn_net *net, int l, int B, float scale, 
         ProfPair pp;
         B2_TRY(prof_begin(net, 1, us, &pp));
         dp::reduce_update_kernel<<<(int)blocks, dp::DP_THREADS, 0, us>>>(a);
-        B2_TRY(prof_end(us, pp));
+        B2_TRY(prof_end(net, us, pp));
         net->launches++;
         B2_CHECK_CUDA(cudaGetLastError());
     } else {
@@ -697,7 +722,7 @@ int wide_join(b2nn_net *net) {
 // all-reduce (data-parallel) and momentum update (S:325-342).  Bottom-up order puts the big early layers'
 // HBM / NVLink work under the remaining gradient GEMMs and leaves only the LAST (smallest) layer's exposed;
 // the next step's forward GEMM of layer l waits just for layer l's update (wide_forward).
-int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
+static int wide_backward_launches(b2nn_net *net, int B, int global_B, double step, double momentum) {
     const int L = net->n_dims - 1;
     const float scale = (float)(step / (double)global_B);  // step*G/batch.size(), S:333
     const float mu = (float)momentum;
@@ -717,6 +742,10 @@ int wide_backward(b2nn_net *net, int B, int global_B, double step, double moment
         B2_TRY(launch_gradient_and_update(net, l, B, scale, mu, us));
     }
     return wide_join(net);
+}
+int wide_backward(b2nn_net *net, int B, int global_B, double step, double momentum) {
+    B2_TRY(wide_backward_launches(net, B, global_B, step, momentum));
+    return prof_close(net);
 }
 
 int wide_eval_rows(b2nn_net *net, int rows, const int32_t *labels_dev, int32_t *pred_dev, bool want_loss) {

@@ -233,7 +233,10 @@ int b2nn_set_stream(b2nn_net *net, void *cuda_stream);
 int b2nn_kernel_launches(const b2nn_net *net, int64_t *n);
 /* Measurement aid: with profiling on, every contraction (GEMM) launch is bracketed by CUDA events
  * on the launching stream; b2nn_profile_read synchronises and returns the summed device time (ms),
- * launch count and algorithmic FLOPs (2*M*N*K per launch) since profiling was switched on. */
+ * launch count and algorithmic FLOPs (2*M*N*K per launch) since profiling was switched on.
+ * on = 1: one event pair per launch; on = 2: one pair around each RUN of consecutive contraction launches on a stream
+ * (a forward pass, the backward GEMMs between two other kernels) -- a timing event between two kernels idles the stream
+ * for several microseconds, so per-launch pairs overstate a ~90 us launch by several percent. */
 int b2nn_profile_enable(b2nn_net *net, int32_t on);
 int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, double *gemm_flops);
 /* the same pass itemised by kernel class: [0] contractions, [1] momentum update / cross-GPU exchange, [2] output delta

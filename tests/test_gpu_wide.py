@@ -364,3 +364,37 @@ def test_fused_update_epilogue_matches_separate_update_kernel(g, prec, dims, B, 
     assert k_f == k_s - 4 * (len(dims) - 1)                 # one update kernel per layer and step fewer
     assert np.linalg.norm(du_f - du_s) <= 1e-6 * np.linalg.norm(du_s)
     assert np.linalg.norm(v_f - v_s) <= 1e-6 * np.linalg.norm(v_s)
+
+
+def test_profile_windows_per_launch_and_per_run(g):
+    """bench.py's roofline instrument (b2nn_profile_enable): mode 1 brackets every contraction launch with its own event
+    pair, mode 2 brackets each RUN of consecutive contraction launches (the forward GEMMs; the backward GEMMs).  Both
+    count the same launches and the same algorithmic FLOPs (2 M N K per launch), neither changes what the step
+    computes, and the per-run windows are fewer than the launches."""
+    dims, B, steps = [512, 384, 256, 100], 256, 3
+    L = len(dims) - 1
+    rng = np.random.RandomState(23)
+    x = rng.rand(B, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], B).astype(np.int32)
+    flops_step = 2.0 * B * (3 * sum(a * b for a, b in zip(dims[:-1], dims[1:])) - dims[0] * dims[1])
+    res = {}
+    for mode in (0, 1, 2):
+        net = wide_net(g, dims)
+        if mode:
+            net.profileEnable(mode)
+        for _ in range(steps):
+            net.gradientStepLabeled(x, lab, 0.05, 0.9)
+        if mode:
+            ms, n, fl = net.profileRead()
+            cls = net.profileReadClasses()
+            net.profileEnable(False)
+            assert n == steps * (3 * L - 1) and fl == steps * flops_step
+            assert ms > 0 and abs(cls["contraction"][0] - ms) <= 1e-9 * ms
+            assert cls["output"][1] == steps
+            res[mode] = (net.getWeights(), cls["contraction"][1])
+        else:
+            res[mode] = (net.getWeights(), 0)
+        net.close()
+    assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][0], res[2][0])
+    assert res[1][1] == steps * (3 * L - 1)      # a window per launch
+    assert res[2][1] == 2 * steps                # forward run + backward run per step
