@@ -83,6 +83,7 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = !(fu != nullptr && fu[0] == '0');   // single-GPU nets; B2NN_FUSED_UPDATE=0: separate update kernel
         net->trace = getenv("B2NN_TRACE") != nullptr;
+        { const char *pd = getenv("B2NN_PDL"); net->pdl = pd != nullptr && pd[0] == '1'; }
         net->dp_ctas = prop.multiProcessorCount;  // one 128-thread CTA per SM beside the GEMM (measured best at 8 GPUs)
         if (const char *dc = getenv("B2NN_DP_CTAS")) { if (atoi(dc) > 0) net->dp_ctas = atoi(dc); }
         if (const char *to = getenv("B2NN_DP_TIMEOUT_MS")) { if (atof(to) > 0) net->dp_timeout_ns = (unsigned long long)(atof(to) * 1e6); }

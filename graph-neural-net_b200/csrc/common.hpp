@@ -180,6 +180,7 @@ struct b2nn_net {
     bool dynamic_tiles_forced = false;
     bool dynamic_tiles = false;  // B2NN_DYNAMIC_TILES=1, or data-parallel (NCCL kernels share the SMs)
     bool backward_reorder = true;  // all deltas first, then gradients bottom-up (B2NN_BACKWARD_REORDER=0: layer by layer)
+    bool pdl = false;            // B2NN_PDL=1: consecutive contraction launches overlap prologue and drain (programmatic dependent launch)
     bool fused_update = true;   // single GPU: momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=0: separate kernel)
     bool overlap_update = true;  // layer l's update on the side stream under layer l-1's GEMMs (B2NN_OVERLAP_UPDATE=0: off)  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;

@@ -489,6 +489,11 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
+    // Programmatic dependent launch (wide_path.cu launches consecutive contractions with it): everything above touched
+    // only this CTA's shared memory, TMEM and the kernel parameters, so it may run while the previous kernel of the
+    // stream is still draining its last tiles on other SMs; from here on global memory is read and written.
+    ptx::grid_dep_launch_dependents();
+    ptx::grid_dep_wait();
 
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================

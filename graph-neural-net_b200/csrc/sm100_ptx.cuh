@@ -125,6 +125,13 @@ __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---- programmatic dependent launch: the NEXT kernel of the stream may start its prologue while this one drains ----
+// launch_dependents: this CTA no longer holds the dependent grid back (it is placed as soon as every CTA of this grid
+// has said so or exited, and an SM has room); wait: returns once the grids this one depends on have completed and their
+// writes are visible.  Both are no-ops in a launch without cudaLaunchAttributeProgrammaticStreamSerialization.
+__device__ __forceinline__ void grid_dep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- CTA pair (cta_group::2): two CTAs of a cluster, one per SM of a TPC, share one MMA ---------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;

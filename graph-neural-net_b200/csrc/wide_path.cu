@@ -189,7 +189,19 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
         B2_CHECK_CUDA(cudaMemsetAsync(stalls_dev, 0, 8 * 148 * 2 * sizeof(unsigned int), net->stream));
         ga.stalls = stalls_dev;
     }
-    kernel<<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
+    if (net->pdl) {
+        // the kernel's prologue (barrier set-up, TMEM allocation, pair rendezvous) may overlap the previous kernel's drain
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(GEMM_THREADS);
+        cfg.dynamicSmemBytes = GEMM_SMEM_BYTES; cfg.stream = net->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        B2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kernel, ta, tb, ga));
+    } else {
+        kernel<<<2 * pairs, GEMM_THREADS, GEMM_SMEM_BYTES, net->stream>>>(ta, tb, ga);
+    }
     if (want_stalls) {
         static int printed = 0;
         std::vector<unsigned int> h(8 * 2 * pairs);
