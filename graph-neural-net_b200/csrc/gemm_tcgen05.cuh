@@ -113,7 +113,7 @@ struct GemmArgs {
     float act_param;
     unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
     unsigned int *stalls;        // debug (B2NN_GEMM_STALLS=1): [cta][8] cycle counters of the role warps, or null
-    int dbg;                     // debug (B2NN_GEMM_DBG): bit 0 = override the TF32 kernel's source-format fields with bits 4-6
+    int dbg;                     // debug (B2NN_GEMM_DBG): bit 1 = release the dependent launch at the kernel start; bit 0 = override the TF32 kernel's source-format fields with bits 4-6
 };
 
 __device__ __forceinline__ float act_apply(int act, float p, float z) {
@@ -492,7 +492,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     // Programmatic dependent launch (wide_path.cu launches consecutive contractions with it): everything above touched
     // only this CTA's shared memory, TMEM and the kernel parameters, so it may run while the previous kernel of the
     // stream is still draining its last tiles on other SMs; from here on global memory is read and written.
-    ptx::grid_dep_launch_dependents();
+    if (g.dbg & 2) ptx::grid_dep_launch_dependents();   // measurement aid: release the dependent grid at the START instead
     ptx::grid_dep_wait();
 
     if (warp == 0) {
@@ -528,6 +528,11 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
                 }
             }
             if (g.stalls) g.stalls[blockIdx.x * 8 + 0] = st_wait;
+            // this CTA has requested its last operand block: the next kernel of the stream may be placed from now on (its
+            // CTAs find room as ours exit).  Released at the start, the pending grid sits at the head of the hardware queue
+            // for the whole kernel and can hold back the other streams' kernels (the host-fed input prologue: end to end
+            // 1.53 instead of 0.80 ms/step in one run of two).
+            ptx::grid_dep_launch_dependents();
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
