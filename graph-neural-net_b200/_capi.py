@@ -59,6 +59,8 @@ SIGNATURES = {
     "b2nn_comm_nvls_bind": (C.c_int, [_vp]),
     "b2nn_comm_mode": (C.c_int, [_vp, _vp]),
     "b2nn_sync": (C.c_int, [_vp]),
+    "b2nn_propagate_device_noalloc": (C.c_int, [_vp, _vp, C.c_int32, _vp]),   # DEVICE pointers
+    "b2nn_noalloc_max_doubles": (C.c_int, [C.POINTER(C.c_int64)]),
     "b2nn_set_stream": (C.c_int, [_vp, _vp]),
     "b2nn_kernel_launches": (C.c_int, [_vp, _lp]),
     "b2nn_profile_enable": (C.c_int, [_vp, C.c_int32]),

@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(LIBDIR, "libb2nn.so")
-SOURCES = ["api.cu", "api_train.cu", "api_data.cu", "f64_path.cu", "f64_fused.cu", "wide_path.cu", "comm.cu", "comm_vmm.cu", "sampler.cu", "checkpoint.cu"]
+SOURCES = ["api.cu", "api_train.cu", "api_data.cu", "f64_path.cu", "f64_fused.cu", "wide_path.cu", "comm.cu", "comm_vmm.cu", "sampler.cu", "checkpoint.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

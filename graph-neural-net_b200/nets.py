@@ -61,6 +61,13 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_propagate(self._h, _d(x), x.shape[0], _d(y)))
         return y[0] if single else y
 
+    def propagateDeviceNoAlloc(self, x_dev_ptr, n, y_dev_ptr):
+        """b2nn_propagate_device_noalloc (no reference counterpart): propagate for FP64 nets over DEVICE buffers
+        (addresses as ints: x [n][d0] in, y [n][dL] out), work rows in the library's fixed 4 MB device array, nothing
+        allocated, launched on the net's stream without a sync (call sync())."""
+        capi.check(capi.lib().b2nn_propagate_device_noalloc(self._h, C.c_void_p(int(x_dev_ptr)), int(n),
+                                                            C.c_void_p(int(y_dev_ptr))))
+
     def calculateLoss(self, input, expected):
         """src/NeuralNet.java:27; batched inputs return one loss per row."""
         x, t = _f64(input), _f64(expected)

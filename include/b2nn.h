@@ -248,6 +248,21 @@ int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4);
  * launch in the order stage, phase1, barrier1, phase2, barrier2, p3:delta2, phase4, p5:W2, p3:a2, p3:z3, p3:softmax,
  * p3:loss, p5:W0, p5:W1c, p5:W1r, stage:wait; steps_or_null its step count.  The call first returns, then sets `on`. */
 int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t *steps_or_null);
+/* ---- allocation-free forward pass --------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * b2nn_propagate_device_noalloc is b2nn_propagate for FP64 nets with DEVICE buffers: x_dev [n][d0] raw inputs in,
+ * y_dev [n][dL] output activations out, launched on the net's stream and NOT synchronised (b2nn_sync or the caller's
+ * own stream order).  It allocates nothing: the work rows (activated inputs, every layer's z and a rows) live in one
+ * fixed device array of B2NN_NOALLOC_MAX_DOUBLES doubles (4 MB) that every GPU loading the library holds until the
+ * process exits.  n rows need about n * (d0 + 2 * (d1 + .. + d(L-1)) + dL) doubles, each sub-buffer rounded up to 32;
+ * more than the array holds -> B2NN_ERR_INVALID_ARG with the numbers in b2nn_last_error; tensor-core nets ->
+ * B2NN_ERR_UNSUPPORTED.  All calls on a device share the array: calls that overlap on the GPU (different streams, two
+ * nets on one device) race; calls on one stream are ordered by it.  Same kernels and summation order as
+ * b2nn_propagate, so the outputs are bit-identical to it. */
+#define B2NN_NOALLOC_MAX_DOUBLES 524288
+int b2nn_propagate_device_noalloc(b2nn_net *net, const double *x_dev, int32_t n, double *y_dev);
+int b2nn_noalloc_max_doubles(int64_t *n);
 int b2nn_device_count(int32_t *n);
 int b2nn_version(void);
 const char *b2nn_last_error(void);
