@@ -83,7 +83,7 @@ int b2nn_create(const int32_t *dims, int32_t n_dims, int32_t net_kind, int32_t i
         const char *fu = getenv("B2NN_FUSED_UPDATE");
         net->fused_update = !(fu != nullptr && fu[0] == '0');   // single-GPU nets; B2NN_FUSED_UPDATE=0: separate update kernel
         net->trace = getenv("B2NN_TRACE") != nullptr;
-        { const char *pd = getenv("B2NN_PDL"); net->pdl = pd != nullptr && pd[0] == '1'; }
+        { const char *pd = getenv("B2NN_PDL"); net->pdl = !(pd != nullptr && pd[0] == '0'); }
         net->dp_ctas = prop.multiProcessorCount;  // one 128-thread CTA per SM beside the GEMM (measured best at 8 GPUs)
         if (const char *dc = getenv("B2NN_DP_CTAS")) { if (atoi(dc) > 0) net->dp_ctas = atoi(dc); }
         if (const char *to = getenv("B2NN_DP_TIMEOUT_MS")) { if (atof(to) > 0) net->dp_timeout_ns = (unsigned long long)(atof(to) * 1e6); }
@@ -144,6 +144,7 @@ int b2nn_destroy(b2nn_net *net) {
     f64_free(net);
     wide_free(net);
     for (auto e : net->prof_events) cudaEventDestroy(e);
+    if (net->prof_stamps) cudaFree(net->prof_stamps);
     if (net->pinned) cudaFreeHost(net->pinned);
     if (net->dscratch) cudaFree(net->dscratch);
     if (net->own_stream && net->stream) cudaStreamDestroy(net->stream);
@@ -209,6 +210,18 @@ int b2nn_kernel_launches(const b2nn_net *net, int64_t *n) {
     return B2NN_OK;
 }
 
+// slots back to (start = max, end = 0), behind whatever the stream still holds
+static int stamps_reset(b2nn_net *net) {
+    const size_t n = (size_t)net->prof_stamp_cap;
+    std::vector<unsigned long long> init(2 * n);
+    for (size_t i = 0; i < n; i++) { init[2 * i] = ~0ull; init[2 * i + 1] = 0ull; }
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    B2_CHECK_CUDA(cudaMemcpy(net->prof_stamps, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    net->prof_stamp_used = 0;
+    net->prof_stamp_flops = 0;
+    return B2NN_OK;
+}
+
 int b2nn_profile_enable(b2nn_net *net, int32_t on) {
     B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
     B2_CHECK_CUDA(cudaSetDevice(net->device));
@@ -218,7 +231,13 @@ int b2nn_profile_enable(b2nn_net *net, int32_t on) {
         for (auto &e : net->prof_events) B2_CHECK_CUDA(cudaEventCreate(&e));
     }
     B2_TRY(profile_flush(net));
-    net->profiling = on != 0;
+    if (on == 3 && net->prof_stamps == nullptr) {
+        net->prof_stamp_cap = 16384;
+        B2_CHECK_CUDA(cudaMalloc(&net->prof_stamps, 2 * sizeof(unsigned long long) * (size_t)net->prof_stamp_cap));
+    }
+    net->prof_stamping = on == 3;
+    if (on == 3) B2_TRY(stamps_reset(net));
+    net->profiling = on == 1 || on == 2;   // mode 3 records no events and serialises nothing
     net->prof_grouped = on == 2;   // one event pair per run of consecutive contraction launches instead of one per launch
     net->prof_flops = 0; net->prof_ms_acc = 0; net->prof_launch_acc = 0;
     for (int c = 0; c < 4; c++) { net->prof_ms_cls[c] = 0; net->prof_n_cls[c] = 0; }
@@ -244,6 +263,36 @@ int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4) {
         if (launches4) launches4[c] = net->prof_n_cls[c];
     }
     return B2NN_OK;
+}
+
+int b2nn_profile_read_stamps(b2nn_net *net, double *busy_ms, double *sum_ms, int64_t *launches, double *flops) {
+    B2_REQUIRE(net != nullptr, B2NN_ERR_INVALID_ARG, "net is null");
+    B2_REQUIRE(net->prof_stamps != nullptr, B2NN_ERR_INVALID_ARG, "b2nn_profile_enable(net, 3) first");
+    B2_CHECK_CUDA(cudaSetDevice(net->device));
+    B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
+    const int n = net->prof_stamp_used;
+    std::vector<unsigned long long> h(2 * (size_t)n);
+    if (n) B2_CHECK_CUDA(cudaMemcpy(h.data(), net->prof_stamps, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    // launches of one stream start in order: fold [start, end] intervals into their union (consecutive launches overlap
+    // under programmatic dependent launch) and their plain sum
+    double busy = 0, sum = 0;
+    unsigned long long cur0 = 0, cur1 = 0;
+    int64_t valid = 0;
+    for (int i = 0; i < n; i++) {
+        const unsigned long long t0 = h[2 * (size_t)i], t1 = h[2 * (size_t)i + 1];
+        if (t1 <= t0) continue;   // a slot whose kernel never ran
+        valid++;
+        sum += (double)(t1 - t0);
+        if (cur1 == 0) { cur0 = t0; cur1 = t1; }
+        else if (t0 <= cur1) { if (t1 > cur1) cur1 = t1; }
+        else { busy += (double)(cur1 - cur0); cur0 = t0; cur1 = t1; }
+    }
+    if (cur1) busy += (double)(cur1 - cur0);
+    if (busy_ms) *busy_ms = busy * 1e-6;
+    if (sum_ms) *sum_ms = sum * 1e-6;
+    if (launches) *launches = valid;
+    if (flops) *flops = net->prof_stamp_flops;
+    return stamps_reset(net);
 }
 
 int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t *steps_or_null) {

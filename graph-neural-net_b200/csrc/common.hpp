@@ -180,7 +180,7 @@ struct b2nn_net {
     bool dynamic_tiles_forced = false;
     bool dynamic_tiles = false;  // B2NN_DYNAMIC_TILES=1, or data-parallel (NCCL kernels share the SMs)
     bool backward_reorder = true;  // all deltas first, then gradients bottom-up (B2NN_BACKWARD_REORDER=0: layer by layer)
-    bool pdl = false;            // B2NN_PDL=1: consecutive contraction launches overlap prologue and drain (programmatic dependent launch)
+    bool pdl = true;             // (B2NN_PDL=0 switches it off) consecutive contraction launches overlap prologue and drain (programmatic dependent launch)
     bool fused_update = true;   // single GPU: momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=0: separate kernel)
     bool overlap_update = true;  // layer l's update on the side stream under layer l-1's GEMMs (B2NN_OVERLAP_UPDATE=0: off)  // momentum update inside the gradient GEMM's epilogue (B2NN_FUSED_UPDATE=1)
     std::vector<b2nn::WideLayer> wide;
@@ -216,6 +216,12 @@ struct b2nn_net {
     // (0 contraction, 1 momentum update / exchange, 2 output delta, 3 input prologue + label gather)
     bool profiling = false;
     bool prof_grouped = false;      // b2nn_profile_enable(net, 2): ONE pair around each run of consecutive contraction launches
+    // b2nn_profile_enable(net, 3): no events, nothing serialised -- every contraction launch stamps %globaltimer (first CTA
+    // in, last CTA out) into its slot; b2nn_profile_read_stamps folds the slots into busy time
+    bool prof_stamping = false;
+    unsigned long long *prof_stamps = nullptr;   // [prof_stamp_cap][2] on the device
+    int prof_stamp_cap = 0, prof_stamp_used = 0;
+    double prof_stamp_flops = 0;
     cudaEvent_t prof_pending = nullptr;       // stop event of the open contraction window (grouped mode), not yet recorded
     cudaStream_t prof_pending_stream = nullptr;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs

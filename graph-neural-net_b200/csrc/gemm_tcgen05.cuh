@@ -113,6 +113,7 @@ struct GemmArgs {
     float act_param;
     unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
     unsigned int *stalls;        // debug (B2NN_GEMM_STALLS=1): [cta][8] cycle counters of the role warps, or null
+    unsigned long long *stamp;   // measurement aid (b2nn_profile_enable 3): [0] <- min %globaltimer at CTA start, [1] <- max at CTA end; or null
     int dbg;                     // debug (B2NN_GEMM_DBG): bit 1 = release the dependent launch at the kernel start; bit 0 = override the TF32 kernel's source-format fields with bits 4-6
 };
 
@@ -456,6 +457,8 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     float4 *epi_stage_base = reinterpret_cast<float4 *>(smem + GEMM_STAGES * GEMM_STAGE_BYTES + 512);
     if (g.tile_counter == nullptr) { ring.static_next = (int)(blockIdx.x >> 1); ring.static_stride = (int)(gridDim.x >> 1); }
 
+    if (g.stamp != nullptr && threadIdx.x == 0) atomicMin(&g.stamp[0], ptx::globaltimer_ns());
+
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int rank = (int)ptx::cluster_ctarank();
@@ -662,6 +665,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
         ptx::tc_fence_after();
         ptx::tmem_dealloc_pair(tmem_base, GEMM_TMEM_COLS);
     }
+    if (g.stamp != nullptr && threadIdx.x == 0) atomicMax(&g.stamp[1], ptx::globaltimer_ns());
 }
 
 template <int EPI, bool A_MN, bool B_MN>

@@ -125,6 +125,12 @@ __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ---- programmatic dependent launch: the NEXT kernel of the stream may start its prologue while this one drains ----
 // launch_dependents: this CTA no longer holds the dependent grid back (it is placed as soon as every CTA of this grid
 // has said so or exited, and an SM has room); wait: returns once the grids this one depends on have completed and their

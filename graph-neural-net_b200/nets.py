@@ -216,6 +216,13 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_k1_profile(self._h, int(on), cyc, C.byref(n)))
         return dict(zip(self.K1_PHASES, [float(c) for c in cyc])), n.value
 
+    def profileReadStamps(self):
+        """(busy_ms, sum_ms, launches, flops) of the contraction launches since profileEnable(3): in-kernel %globaltimer
+        stamps, no events, nothing serialised"""
+        busy, tot, n, fl = C.c_double(), C.c_double(), C.c_int64(), C.c_double()
+        capi.check(capi.lib().b2nn_profile_read_stamps(self._h, C.byref(busy), C.byref(tot), C.byref(n), C.byref(fl)))
+        return busy.value, tot.value, n.value, fl.value
+
     def profileReadClasses(self):
         """{class: (ms, launches)} of the profiled pass: contraction, update, output, prologue"""
         ms, n = (C.c_double * 4)(), (C.c_int64 * 4)()

@@ -243,6 +243,11 @@ int b2nn_profile_read(b2nn_net *net, double *gemm_ms, int64_t *gemm_launches, do
  * (softmax-CE gradient), [3] input prologue: summed device time (ms) and launch count of each since profiling was
  * switched on (the side-stream work is serialised while profiling, so every kernel is timed alone) */
 int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4);
+/* on = 3: no events and nothing serialised (side-stream work and dependent launches overlap as in production): every
+ * contraction launch stamps %globaltimer, first CTA in / last CTA out, into its own slot (16384 slots per enable/read).
+ * b2nn_profile_read_stamps synchronises and returns the UNION of those intervals (ms the stream spent inside
+ * contractions), their plain sum, the launch count and the algorithmic FLOPs, and clears the slots. */
+int b2nn_profile_read_stamps(b2nn_net *net, double *busy_ms, double *sum_ms, int64_t *launches, double *flops);
 /* Measurement aid for K1 (the persistent fused FP64 training kernel): while `on`, every K1 launch collects the cycle
  * counters of CTA 0 per phase (and synchronises); cycles16_or_null receives the per-step averages of the LAST such
  * launch in the order stage, phase1, barrier1, phase2, barrier2, p3:delta2, phase4, p5:W2, p3:a2, p3:z3, p3:softmax,

@@ -398,3 +398,32 @@ def test_profile_windows_per_launch_and_per_run(g):
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][0], res[2][0])
     assert res[1][1] == steps * (3 * L - 1)      # a window per launch
     assert res[2][1] == 2 * steps                # forward run + backward run per step
+
+
+def test_profile_in_kernel_stamps(g):
+    """b2nn_profile_enable(net, 3): no events; each contraction launch stamps %globaltimer (first CTA in, last CTA out).
+    Every launch is seen, the union of the intervals is positive and no longer than their sum, the FLOPs are the
+    algorithmic ones, the step computes the same bits, and a second read starts from cleared slots."""
+    dims, B, steps = [512, 384, 256, 100], 256, 3
+    L = len(dims) - 1
+    rng = np.random.RandomState(29)
+    x = rng.rand(B, dims[0]).astype(np.float32)
+    lab = rng.randint(0, dims[-1], B).astype(np.int32)
+    flops_step = 2.0 * B * (3 * sum(a * b for a, b in zip(dims[:-1], dims[1:])) - dims[0] * dims[1])
+    ws = []
+    for mode in (0, 3):
+        net = wide_net(g, dims)
+        if mode:
+            net.profileEnable(3)
+        for _ in range(steps):
+            net.gradientStepLabeled(x, lab, 0.05, 0.9)
+        if mode:
+            busy, tot, n, fl = net.profileReadStamps()
+            assert n == steps * (3 * L - 1) and fl == steps * flops_step
+            assert 0 < busy <= tot * (1 + 1e-12)
+            assert tot / n < 1.0                        # ms per launch of these small contractions: sane clock units
+            assert net.profileReadStamps()[2] == 0      # cleared
+            net.profileEnable(False)
+        ws.append(net.getWeights())
+        net.close()
+    assert np.array_equal(ws[0], ws[1])
