@@ -401,6 +401,7 @@ def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, wan
     train_call(g, net, ds_dev, idx_time, B, step)
     e5.record(ctx.stream)
     busy_ms, stamp_sum_ms, stamp_n, stamp_flops = net.profileReadStamps()
+    stamp_mhz = net.profileStampClockMHz()
     net.profileEnable(False)
     stamp_step_ms = e4.elapsed_time(e5) / K
     pk = measured_peaks(tf32)
@@ -429,6 +430,9 @@ def measure_wide(ctx, name, tf32, K, W, want_e2e=True, want_sustained=False, wan
                             "frac_burst": stamp_flops / max(busy_ms, 1e-9) / 1e9 / pk["burst"],
                             "frac_sustained": stamp_flops / max(busy_ms, 1e-9) / 1e9 / pk["sustained"],
                             "step_ms": stamp_step_ms,
+                            # cycles / ns of CTA 0 of every launch: the SM clock the timed steps really ran at (nvidia-smi
+                            # samples every ~20 ms and misses what the power cap does inside a 36 ms region)
+                            "sm_mhz_effective": stamp_mhz,
                             "how": "b2nn_profile_enable(3): every contraction launch records %globaltimer at its first CTA's "
                                    "start and its last CTA's end; busy = union of the intervals, nothing serialised"},
         "flops_per_step": fl_step_gpu, "gemm_share_of_step": (gemm_ms / K) / prof_step_ms,

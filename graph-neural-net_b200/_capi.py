@@ -67,6 +67,7 @@ SIGNATURES = {
     "b2nn_profile_read": (C.c_int, [_vp, _dp, _lp, _dp]),
     "b2nn_profile_read_classes": (C.c_int, [_vp, _dp, _lp]),
     "b2nn_profile_read_stamps": (C.c_int, [_vp, _dp, _dp, C.POINTER(C.c_int64), _dp]),
+    "b2nn_profile_stamp_clock_mhz": (C.c_int, [_vp, _dp]),
     "b2nn_k1_profile": (C.c_int, [_vp, C.c_int32, _dp, _ip]),
     "b2nn_device_count": (C.c_int, [_ip]),
     "b2nn_version": (C.c_int, []),

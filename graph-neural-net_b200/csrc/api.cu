@@ -213,8 +213,8 @@ int b2nn_kernel_launches(const b2nn_net *net, int64_t *n) {
 // slots back to (start = max, end = 0), behind whatever the stream still holds
 static int stamps_reset(b2nn_net *net) {
     const size_t n = (size_t)net->prof_stamp_cap;
-    std::vector<unsigned long long> init(2 * n);
-    for (size_t i = 0; i < n; i++) { init[2 * i] = ~0ull; init[2 * i + 1] = 0ull; }
+    std::vector<unsigned long long> init(4 * n, 0ull);
+    for (size_t i = 0; i < n; i++) init[4 * i] = ~0ull;
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     B2_CHECK_CUDA(cudaMemcpy(net->prof_stamps, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
     net->prof_stamp_used = 0;
@@ -233,7 +233,7 @@ int b2nn_profile_enable(b2nn_net *net, int32_t on) {
     B2_TRY(profile_flush(net));
     if (on == 3 && net->prof_stamps == nullptr) {
         net->prof_stamp_cap = 16384;
-        B2_CHECK_CUDA(cudaMalloc(&net->prof_stamps, 2 * sizeof(unsigned long long) * (size_t)net->prof_stamp_cap));
+        B2_CHECK_CUDA(cudaMalloc(&net->prof_stamps, 4 * sizeof(unsigned long long) * (size_t)net->prof_stamp_cap));
     }
     net->prof_stamping = on == 3;
     if (on == 3) B2_TRY(stamps_reset(net));
@@ -271,17 +271,18 @@ int b2nn_profile_read_stamps(b2nn_net *net, double *busy_ms, double *sum_ms, int
     B2_CHECK_CUDA(cudaSetDevice(net->device));
     B2_CHECK_CUDA(cudaStreamSynchronize(net->stream));
     const int n = net->prof_stamp_used;
-    std::vector<unsigned long long> h(2 * (size_t)n);
+    std::vector<unsigned long long> h(4 * (size_t)n);
     if (n) B2_CHECK_CUDA(cudaMemcpy(h.data(), net->prof_stamps, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     // launches of one stream start in order: fold [start, end] intervals into their union (consecutive launches overlap
     // under programmatic dependent launch) and their plain sum
-    double busy = 0, sum = 0;
+    double busy = 0, sum = 0, clk = 0, clk_ns = 0;
     unsigned long long cur0 = 0, cur1 = 0;
     int64_t valid = 0;
     for (int i = 0; i < n; i++) {
-        const unsigned long long t0 = h[2 * (size_t)i], t1 = h[2 * (size_t)i + 1];
+        const unsigned long long t0 = h[4 * (size_t)i], t1 = h[4 * (size_t)i + 1];
         if (t1 <= t0) continue;   // a slot whose kernel never ran
         valid++;
+        clk += (double)h[4 * (size_t)i + 2]; clk_ns += (double)h[4 * (size_t)i + 3];
         sum += (double)(t1 - t0);
         if (cur1 == 0) { cur0 = t0; cur1 = t1; }
         else if (t0 <= cur1) { if (t1 > cur1) cur1 = t1; }
@@ -292,7 +293,14 @@ int b2nn_profile_read_stamps(b2nn_net *net, double *busy_ms, double *sum_ms, int
     if (sum_ms) *sum_ms = sum * 1e-6;
     if (launches) *launches = valid;
     if (flops) *flops = net->prof_stamp_flops;
+    net->prof_stamp_mhz = clk_ns > 0 ? clk / clk_ns * 1e3 : 0.0;
     return stamps_reset(net);
+}
+
+int b2nn_profile_stamp_clock_mhz(const b2nn_net *net, double *mhz) {
+    B2_REQUIRE(net != nullptr && mhz != nullptr, B2NN_ERR_INVALID_ARG, "null argument");
+    *mhz = net->prof_stamp_mhz;
+    return B2NN_OK;
 }
 
 int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t *steps_or_null) {

@@ -222,6 +222,7 @@ struct b2nn_net {
     unsigned long long *prof_stamps = nullptr;   // [prof_stamp_cap][2] on the device
     int prof_stamp_cap = 0, prof_stamp_used = 0;
     double prof_stamp_flops = 0;
+    double prof_stamp_mhz = 0;    // SM clock of the stamped launches of the last b2nn_profile_read_stamps (cycles / ns of CTA 0)
     cudaEvent_t prof_pending = nullptr;       // stop event of the open contraction window (grouped mode), not yet recorded
     cudaStream_t prof_pending_stream = nullptr;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs

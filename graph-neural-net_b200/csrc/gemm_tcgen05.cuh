@@ -57,6 +57,16 @@ constexpr int GEMM_STAGES = B2NN_GEMM_STAGES;   // 5 x 32 KB operand stages + 32
 #endif
 constexpr int GEMM_EPI_WARPS = B2NN_GEMM_EPI_WARPS;   // GEMM_EPI_PARTS warps per TMEM lane quarter, each draining 1/PARTS of the columns
 constexpr int GEMM_EPI_PARTS = GEMM_EPI_WARPS / 4;
+#ifndef B2NN_GEMM_EPI_PIPE
+#define B2NN_GEMM_EPI_PIPE 1
+#endif
+#ifndef B2NN_GEMM_BAND
+#define B2NN_GEMM_BAND 8
+#endif
+// tile order: bands of GEMM_BAND tile rows, column by column inside a band (1 = plain row-major order)
+constexpr int GEMM_BAND = B2NN_GEMM_BAND;
+constexpr int GEMM_EPI_PIPE = B2NN_GEMM_EPI_PIPE;   // epilogue look-ahead: 0 none, 1 the aux loads of EPI_DX one chunk ahead (the TMEM reads one chunk
+                                                    // ahead too cost 64 registers and the host-fed pipeline its co-residency: measured, rejected)
 static_assert(GEMM_EPI_WARPS % 4 == 0 && (GEMM_EPI_PARTS == 1 || GEMM_EPI_PARTS == 2 || GEMM_EPI_PARTS == 4),
               "epilogue warps come in groups of four (one per TMEM lane quarter); 128-column half tiles split into <= 4 parts of 32");
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
@@ -113,7 +123,8 @@ struct GemmArgs {
     float act_param;
     unsigned int *tile_counter;  // work-item counter of the dynamic scheduler (0 at launch, reset by the kernel)
     unsigned int *stalls;        // debug (B2NN_GEMM_STALLS=1): [cta][8] cycle counters of the role warps, or null
-    unsigned long long *stamp;   // measurement aid (b2nn_profile_enable 3): [0] <- min %globaltimer at CTA start, [1] <- max at CTA end; or null
+    unsigned long long *stamp;   // measurement aid (b2nn_profile_enable 3): [0] <- min %globaltimer at CTA start, [1] <- max at CTA end,
+                                 // [2] / [3] <- CTA 0's lifetime in SM cycles / in nanoseconds; or null
     int dbg;                     // debug (B2NN_GEMM_DBG): bit 1 = release the dependent launch at the kernel start; bit 0 = override the TF32 kernel's source-format fields with bits 4-6
 };
 
@@ -223,8 +234,30 @@ __device__ __forceinline__ void dx32_f32(const float *arow, int n0, int N, const
     }
 }
 
+// the 32 stored activations a = f(z) of row m, columns n0..n0+31, packed BF16 (zeros beyond the edges): the aux operand
+// of the BF16 EPI_DX epilogue.  Does not depend on the accumulator, so the epilogue warps issue it one chunk AHEAD.
+__device__ __forceinline__ void load_aux_bf16(const GemmArgs &g, int m, int n0, uint4 (&u)[4]) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) u[q] = make_uint4(0u, 0u, 0u, 0u);
+    if (m >= g.M || n0 >= g.N) return;
+    const __nv_bfloat16 *arow = reinterpret_cast<const __nv_bfloat16 *>(g.aux) + (size_t)m * g.ldaux + n0;
+    if (n0 + 32 <= g.N) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) u[q] = reinterpret_cast<const uint4 *>(arow)[q];
+    } else {
+        uint32_t *uw = reinterpret_cast<uint32_t *>(u);
+#pragma unroll
+        for (int c = 0; c < 32; c += 2) {
+            const float lo = (n0 + c < g.N) ? __bfloat162float(arow[c]) : 0.f;
+            const float hi = (n0 + c + 1 < g.N) ? __bfloat162float(arow[c + 1]) : 0.f;
+            uw[c >> 1] = pack_bf16x2(lo, hi);
+        }
+    }
+}
+
+// `u`: the chunk's aux values from load_aux_bf16 (BF16 EPI_DX only; ignored by every other epilogue)
 template <int EPI, bool TF32>
-__device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0, const uint32_t (&r)[32]) {
+__device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0, const uint32_t (&r)[32], const uint4 (&u)[4]) {
     if (m >= g.M || n0 >= g.N) return;
     if constexpr (EPI == EPI_ACT) {
         float x[32];
@@ -266,20 +299,6 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs &g, int m, int n0,
         }
         store_f32_row(reinterpret_cast<float *>(g.out0), g.ld0, g.N, m, n0, x);
     } else if constexpr (EPI == EPI_DX) {
-        const __nv_bfloat16 *arow = reinterpret_cast<const __nv_bfloat16 *>(g.aux) + (size_t)m * g.ldaux + n0;
-        uint4 u[4];  // the 32 stored activations a = f(z), packed BF16
-        if (n0 + 32 <= g.N) {
-#pragma unroll
-            for (int q = 0; q < 4; q++) u[q] = reinterpret_cast<const uint4 *>(arow)[q];
-        } else {
-            uint32_t *uw = reinterpret_cast<uint32_t *>(u);
-#pragma unroll
-            for (int c = 0; c < 32; c += 2) {
-                const float lo = (n0 + c < g.N) ? __bfloat162float(arow[c]) : 0.f;
-                const float hi = (n0 + c + 1 < g.N) ? __bfloat162float(arow[c + 1]) : 0.f;
-                uw[c >> 1] = pack_bf16x2(lo, hi);
-            }
-        }
         float x[32];
         switch (g.act) {  // one branch per 32 columns; f' from the stored activation
         case ACT_LEAKY_RELU: { const float p = g.act_param; dx32(u, r, x, [p](float a) { return a > 0.f ? 1.f : p; }); break; }
@@ -386,10 +405,15 @@ __device__ __forceinline__ void epilogue_update_prefetch(const GemmArgs &g, int 
 
 // Work list of one launch: items [0, full) are 256 x 256 tiles in row-major tile order, items
 // [full, total) are the 256 x 128 halves of the remaining tiles (see "Wave quantisation" above).
+// Tile order.  The pairs work on ~74 consecutive items at a time and march through K together, so what a wave pulls from
+// HBM is (distinct tile rows + distinct tile columns among those items) x K.  In row-major order 74 items are 2-3 whole
+// rows of an 8192-wide layer: 3 + 32 operand slabs per wave (C5: every forward GEMM streams the 134 MB weight matrix 55
+// times, ~2.3 TB/s of HBM traffic beside the tensor cores).  In bands of GEMM_BAND = 8 tile rows walked column by column
+// the same 74 items are an 8 x 9.25 patch: 8 + 10 slabs, and the band's 8 row slabs stay in L2 until the band is done.
 struct TileSched {
-    int n_tiles, full, total;
+    int n_tiles, m_tiles, full, total;
     __device__ __forceinline__ TileSched(int M, int N, int pairs) {
-        const int m_tiles = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
+        m_tiles = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
         n_tiles = (N + GEMM_BN - 1) / GEMM_BN;
         const int T = m_tiles * n_tiles, rem = T % pairs;
         if (rem > 0 && 2 * rem <= pairs) { full = T - rem; total = T + rem; }
@@ -400,8 +424,15 @@ struct TileSched {
         int t = item, half = 0;
         bn = GEMM_BN;
         if (item >= full) { t = full + ((item - full) >> 1); half = (item - full) & 1; bn = GEMM_BN / 2; }
-        m0 = (t / n_tiles) * (2 * GEMM_BM);
-        n0 = (t % n_tiles) * GEMM_BN + half * (GEMM_BN / 2);
+        int mt, nt;
+        if constexpr (GEMM_BAND <= 1) { mt = t / n_tiles; nt = t % n_tiles; }
+        else {
+            const int per_band = GEMM_BAND * n_tiles, band = t / per_band, idx = t - band * per_band;
+            const int r0 = band * GEMM_BAND, rows = min(GEMM_BAND, m_tiles - r0);   // the last band may be shorter
+            nt = idx / rows; mt = r0 + idx - nt * rows;
+        }
+        m0 = mt * (2 * GEMM_BM);
+        n0 = nt * GEMM_BN + half * (GEMM_BN / 2);
     }
 };
 
@@ -458,6 +489,10 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
     if (g.tile_counter == nullptr) { ring.static_next = (int)(blockIdx.x >> 1); ring.static_stride = (int)(gridDim.x >> 1); }
 
     if (g.stamp != nullptr && threadIdx.x == 0) atomicMin(&g.stamp[0], ptx::globaltimer_ns());
+    // ... and CTA 0 times itself in SM cycles and in nanoseconds: cycles / ns = the SM clock this launch really ran at
+    long long stamp_c0 = 0;
+    unsigned long long stamp_t0 = 0;
+    if (g.stamp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) { stamp_c0 = clock64(); stamp_t0 = ptx::globaltimer_ns(); }
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -632,23 +667,52 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
             if constexpr (EPI == EPI_DW_UPDATE)   // while the tile's main loop runs
                 epilogue_update_prefetch(g, lane, m0 + rank * GEMM_BM + q * 32, n0 + part * (bn / GEMM_EPI_PARTS),
                                          bn / GEMM_EPI_PARTS);
+            const int m = m0 + rank * GEMM_BM + q * 32 + lane;
+            const int cbeg = part * (bn / GEMM_EPI_PARTS), cend = cbeg + bn / GEMM_EPI_PARTS;
+            // BF16 EPI_DX reads the stored activations of the tile (aux): they do not depend on the accumulator, so the
+            // first chunk's are requested while the tile's main loop is still running and every later chunk's one chunk
+            // ahead (ua / ub alternate; no copies)
+            constexpr bool AUX = (EPI == EPI_DX) && !TF32 && GEMM_EPI_PIPE >= 1;
+            uint4 ua[4], ub[4];
+            if constexpr (AUX) load_aux_bf16(g, m, n0 + cbeg, ua);
             const uint32_t c0 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::mbar_wait(&tfull_bar[acc], acc_phase);
             const uint32_t c1 = g.stalls ? (uint32_t)clock64() : 0u;
             ptx::tc_fence_after();
-            const int m = m0 + rank * GEMM_BM + q * 32 + lane;
-            const int cbeg = part * (bn / GEMM_EPI_PARTS), cend = cbeg + bn / GEMM_EPI_PARTS;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * GEMM_BN;
+            if constexpr (EPI == EPI_DW_UPDATE || GEMM_EPI_PIPE == 0) {
 #pragma unroll 1
-            for (int c0 = cbeg; c0 < cend; c0 += 32) {
-                uint32_t r[32];
-                ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
-                ptx::tmem_ld_wait();
-                if constexpr (EPI == EPI_DW_UPDATE)
-                    epilogue_update_chunk<TF32>(g, epi_stage_base + (size_t)(warp - 2) * (GEMM_EPI_STAGE_BYTES / 16), lane,
-                                                m0 + rank * GEMM_BM + q * 32, n0 + c0, r);
-                else
-                    epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r);
+                for (int c0 = cbeg; c0 < cend; c0 += 32) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
+                    ptx::tmem_ld_wait();
+                    if constexpr (EPI == EPI_DW_UPDATE)
+                        epilogue_update_chunk<TF32>(g, epi_stage_base + (size_t)(warp - 2) * (GEMM_EPI_STAGE_BYTES / 16), lane,
+                                                    m0 + rank * GEMM_BM + q * 32, n0 + c0, r);
+                    else {
+                        if constexpr (EPI == EPI_DX && !TF32) load_aux_bf16(g, m, n0 + c0, ua);
+                        epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r, ua);
+                    }
+                }
+            } else {
+                // one accumulator chunk at a time; only the aux loads run ahead, so a chunk of EPI_DX no longer pays a TMEM
+                // round trip AND a memory round trip before its first store (measured: 11.8 K -> 11.0 K busy cycles per
+                // 256 x 256 tile; the K = 1000 delta GEMM, whose main loop is 8.2 K cycles per tile, 49.9 K -> 49.3 K)
+#pragma unroll 1
+                for (int c0 = cbeg; c0 < cend; c0 += 64) {
+                    const bool second = c0 + 32 < cend, third = c0 + 64 < cend;
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, r);
+                    if constexpr (AUX) { if (second) load_aux_bf16(g, m, n0 + c0 + 32, ub); }
+                    ptx::tmem_ld_wait();
+                    epilogue_chunk<EPI, TF32>(g, m, n0 + c0, r, ua);
+                    if (second) {
+                        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)(c0 + 32), r);
+                        if constexpr (AUX) { if (third) load_aux_bf16(g, m, n0 + c0 + 64, ua); }
+                        ptx::tmem_ld_wait();
+                        epilogue_chunk<EPI, TF32>(g, m, n0 + c0 + 32, r, ub);
+                    }
+                }
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -666,6 +730,10 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap &tmA, const CUt
         ptx::tmem_dealloc_pair(tmem_base, GEMM_TMEM_COLS);
     }
     if (g.stamp != nullptr && threadIdx.x == 0) atomicMax(&g.stamp[1], ptx::globaltimer_ns());
+    if (g.stamp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        g.stamp[2] = (unsigned long long)(clock64() - stamp_c0);
+        g.stamp[3] = ptx::globaltimer_ns() - stamp_t0;
+    }
 }
 
 template <int EPI, bool A_MN, bool B_MN>

@@ -182,7 +182,7 @@ static int launch_gemm_t(b2nn_net *net, const CUtensorMap &ta, const CUtensorMap
     static const int gemm_dbg = getenv("B2NN_GEMM_DBG") ? atoi(getenv("B2NN_GEMM_DBG")) : 0;  // bring-up aid
     ga.dbg = gemm_dbg;
     if (net->prof_stamping && net->prof_stamp_used < net->prof_stamp_cap) {
-        ga.stamp = net->prof_stamps + 2 * (size_t)net->prof_stamp_used++;
+        ga.stamp = net->prof_stamps + 4 * (size_t)net->prof_stamp_used++;
         net->prof_stamp_flops += 2.0 * (double)g.M * (double)g.N * (double)g.K;
     }
     static const bool want_stalls = getenv("B2NN_GEMM_STALLS") != nullptr;  // debug: where the role warps wait

@@ -223,6 +223,12 @@ class NeuralNet:
         capi.check(capi.lib().b2nn_profile_read_stamps(self._h, C.byref(busy), C.byref(tot), C.byref(n), C.byref(fl)))
         return busy.value, tot.value, n.value, fl.value
 
+    def profileStampClockMHz(self):
+        """SM clock (MHz) the launches of the last profileReadStamps() ran at: cycles / ns of CTA 0 of every launch"""
+        mhz = C.c_double()
+        capi.check(capi.lib().b2nn_profile_stamp_clock_mhz(self._h, C.byref(mhz)))
+        return mhz.value
+
     def profileReadClasses(self):
         """{class: (ms, launches)} of the profiled pass: contraction, update, output, prologue"""
         ms, n = (C.c_double * 4)(), (C.c_int64 * 4)()

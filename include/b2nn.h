@@ -248,6 +248,11 @@ int b2nn_profile_read_classes(b2nn_net *net, double *ms4, int64_t *launches4);
  * b2nn_profile_read_stamps synchronises and returns the UNION of those intervals (ms the stream spent inside
  * contractions), their plain sum, the launch count and the algorithmic FLOPs, and clears the slots. */
 int b2nn_profile_read_stamps(b2nn_net *net, double *busy_ms, double *sum_ms, int64_t *launches, double *flops);
+/* the SM clock the stamped launches really ran at (MHz): CTA 0 of every launch counts its own lifetime in SM cycles
+ * (%clock64) and in nanoseconds (%globaltimer); this is sum(cycles) / sum(ns) over the launches of the LAST
+ * b2nn_profile_read_stamps.  nvidia-smi samples every ~20 ms and cannot see a 36 ms timed region.  (Measurement export,
+ * no counterpart in the reference.) */
+int b2nn_profile_stamp_clock_mhz(const b2nn_net *net, double *mhz);
 /* Measurement aid for K1 (the persistent fused FP64 training kernel): while `on`, every K1 launch collects the cycle
  * counters of CTA 0 per phase (and synchronises); cycles16_or_null receives the per-step averages of the LAST such
  * launch in the order stage, phase1, barrier1, phase2, barrier2, p3:delta2, phase4, p5:W2, p3:a2, p3:z3, p3:softmax,

@@ -422,6 +422,7 @@ def test_profile_in_kernel_stamps(g):
             assert n == steps * (3 * L - 1) and fl == steps * flops_step
             assert 0 < busy <= tot * (1 + 1e-12)
             assert tot / n < 1.0                        # ms per launch of these small contractions: sane clock units
+            assert 300.0 < net.profileStampClockMHz() < 3000.0   # CTA 0's cycles / ns: an SM clock
             assert net.profileReadStamps()[2] == 0      # cleared
             net.profileEnable(False)
         ws.append(net.getWeights())
