@@ -69,6 +69,7 @@ SIGNATURES = {
     "b2nn_profile_read_stamps": (C.c_int, [_vp, _dp, _dp, C.POINTER(C.c_int64), _dp]),
     "b2nn_profile_stamp_clock_mhz": (C.c_int, [_vp, _dp]),
     "b2nn_k1_profile": (C.c_int, [_vp, C.c_int32, _dp, _ip]),
+    "b2nn_debug_tile_list": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, _ip, _ip, _ip, C.c_int32, _ip]),
     "b2nn_device_count": (C.c_int, [_ip]),
     "b2nn_version": (C.c_int, []),
     "b2nn_last_error": (C.c_char_p, []),

@@ -25,6 +25,11 @@ extern "C" {
 const char *b2nn_last_error(void) { return get_error(); }
 int b2nn_version(void) { return B2NN_VERSION; }
 
+int b2nn_debug_tile_list(int32_t M, int32_t N, int32_t pairs, int32_t *m0, int32_t *n0, int32_t *bn, int32_t cap,
+                         int32_t *total) {
+    return wide_tile_list(M, N, pairs, m0, n0, bn, cap, total);
+}
+
 int b2nn_device_count(int32_t *n) {
     B2_REQUIRE(n != nullptr, B2NN_ERR_INVALID_ARG, "n is null");
     int c = 0;

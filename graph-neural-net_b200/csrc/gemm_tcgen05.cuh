@@ -412,7 +412,7 @@ __device__ __forceinline__ void epilogue_update_prefetch(const GemmArgs &g, int 
 // the same 74 items are an 8 x 9.25 patch: 8 + 10 slabs, and the band's 8 row slabs stay in L2 until the band is done.
 struct TileSched {
     int n_tiles, m_tiles, full, total;
-    __device__ __forceinline__ TileSched(int M, int N, int pairs) {
+    __host__ __device__ __forceinline__ TileSched(int M, int N, int pairs) {
         m_tiles = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
         n_tiles = (N + GEMM_BN - 1) / GEMM_BN;
         const int T = m_tiles * n_tiles, rem = T % pairs;
@@ -420,7 +420,7 @@ struct TileSched {
         else { full = T; total = T; }
     }
     // -> first row / column of the pair's tile and its width (256 or 128)
-    __device__ __forceinline__ void decode(int item, int &m0, int &n0, int &bn) const {
+    __host__ __device__ __forceinline__ void decode(int item, int &m0, int &n0, int &bn) const {
         int t = item, half = 0;
         bn = GEMM_BN;
         if (item >= full) { t = full + ((item - full) >> 1); half = (item - full) & 1; bn = GEMM_BN / 2; }
@@ -428,7 +428,7 @@ struct TileSched {
         if constexpr (GEMM_BAND <= 1) { mt = t / n_tiles; nt = t % n_tiles; }
         else {
             const int per_band = GEMM_BAND * n_tiles, band = t / per_band, idx = t - band * per_band;
-            const int r0 = band * GEMM_BAND, rows = min(GEMM_BAND, m_tiles - r0);   // the last band may be shorter
+            const int r0 = band * GEMM_BAND, left = m_tiles - r0, rows = left < GEMM_BAND ? left : GEMM_BAND;   // the last band may be shorter
             nt = idx / rows; mt = r0 + idx - nt * rows;
         }
         m0 = mt * (2 * GEMM_BM);

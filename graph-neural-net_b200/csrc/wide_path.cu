@@ -809,4 +809,19 @@ int wide_gather_targets(b2nn_net *net, const double *T, const int32_t *idx_dev, 
     return B2NN_OK;
 }
 
+// the work list of one contraction launch, exactly as the kernel's role warps decode it (b2nn_debug_tile_list)
+int wide_tile_list(int M, int N, int pairs, int32_t *m0, int32_t *n0, int32_t *bn, int cap, int32_t *total) {
+    B2_REQUIRE(M > 0 && N > 0 && pairs > 0 && total != nullptr, B2NN_ERR_INVALID_ARG, "M, N, pairs must be positive");
+    const TileSched sched(M, N, pairs);
+    *total = sched.total;
+    for (int item = 0; item < sched.total && item < cap; item++) {
+        int a, b, c;
+        sched.decode(item, a, b, c);
+        if (m0) m0[item] = a;
+        if (n0) n0[item] = b;
+        if (bn) bn[item] = c;
+    }
+    return B2NN_OK;
+}
+
 }  // namespace b2nn

@@ -27,5 +27,6 @@ int wide_propagate_rows(b2nn_net *net, int rows, double *P_dev);
 int wide_reduce(b2nn_net *net, int rows, const int32_t *pred_dev, const int32_t *labels_dev, double *loss_sum_dev,
                 long long *hits_dev);
 int wide_gather_labels(b2nn_net *net, const int32_t *labels, const int32_t *idx_dev, int B, cudaStream_t st);
+int wide_tile_list(int M, int N, int pairs, int32_t *m0, int32_t *n0, int32_t *bn, int cap, int32_t *total);
 int wide_gather_targets(b2nn_net *net, const double *T, const int32_t *idx_dev, int B);
 }  // namespace b2nn

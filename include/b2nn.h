@@ -273,6 +273,13 @@ int b2nn_k1_profile(b2nn_net *net, int32_t on, double *cycles16_or_null, int32_t
 #define B2NN_NOALLOC_MAX_DOUBLES 524288
 int b2nn_propagate_device_noalloc(b2nn_net *net, const double *x_dev, int32_t n, double *y_dev);
 int b2nn_noalloc_max_doubles(int64_t *n);
+/* Debug export (host only, no GPU needed, no counterpart in the reference): the work list of one tensor-core contraction
+ * launch D[M][N] on `pairs` CTA pairs, exactly as the kernel decodes it -- item i is the output tile whose first row /
+ * column are m0[i] / n0[i] and whose width is bn[i] (256, or 128 for the halves the last partial wave is split into); the
+ * order is the banded one (bands of 8 tile rows, column by column).  Writes min(*total, cap) entries; any of the arrays
+ * may be null.  tests/test_capi_cpu.py checks on the CPU that every output element is covered exactly once. */
+int b2nn_debug_tile_list(int32_t M, int32_t N, int32_t pairs, int32_t *m0, int32_t *n0, int32_t *bn, int32_t cap,
+                         int32_t *total);
 int b2nn_device_count(int32_t *n);
 int b2nn_version(void);
 const char *b2nn_last_error(void);

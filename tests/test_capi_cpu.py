@@ -120,3 +120,39 @@ def test_pixel_byte_quotient_float_equals_double():
     b = np.arange(256)
     assert np.array_equal((b.astype(np.float32) / np.float32(255.0)).astype(np.float32),
                           (b.astype(np.float64) / 255.0).astype(np.float32))
+
+
+@pytest.mark.parametrize("M,N,pairs", [(4096, 4096, 74), (4096, 1000, 74), (32768, 8192, 74), (8192, 8192, 74),
+                                        (300, 264, 74), (37, 8, 74), (2560, 2048, 74), (4096, 4096, 8), (2304, 512, 5),
+                                        (256 * 9, 256 * 3, 74), (256 * 17, 256 * 5, 37), (1, 1, 1)])
+def test_tile_order_covers_every_output_once(g, M, N, pairs):
+    """The contraction kernel's work list (TileSched in gemm_tcgen05.cuh, decoded on the host through
+    b2nn_debug_tile_list): bands of 8 tile rows walked column by column, the last partial wave split into 256 x 128
+    halves.  Every 256 x 256 output tile must appear exactly once -- whole, or as its two halves -- whatever the
+    shape (ragged edges, fewer than 8 tile rows, a short last band), and the items a wave of `pairs` pairs holds at a time
+    must share operand slabs the way the order promises."""
+    lib = g.capi.lib()
+    total = C.c_int32()
+    g.capi.check(lib.b2nn_debug_tile_list(M, N, pairs, None, None, None, 0, C.byref(total)))
+    n = total.value
+    m0, n0, bn = (np.empty(n, np.int32) for _ in range(3))
+    ip = C.POINTER(C.c_int32)
+    g.capi.check(lib.b2nn_debug_tile_list(M, N, pairs, m0.ctypes.data_as(ip), n0.ctypes.data_as(ip),
+                                          bn.ctypes.data_as(ip), n, C.byref(total)))
+    m_tiles, n_tiles = -(-M // 256), -(-N // 256)
+    cover = np.zeros((m_tiles, 2 * n_tiles), np.int32)          # in units of 128 columns
+    for a, b, w in zip(m0, n0, bn):
+        assert a % 256 == 0 and b % 128 == 0 and w in (128, 256) and 0 <= a < m_tiles * 256 and 0 <= b < n_tiles * 256
+        assert w == 128 or b % 256 == 0
+        cover[a // 256, b // 128: b // 128 + w // 128] += 1
+    assert (cover == 1).all()
+    T = m_tiles * n_tiles
+    rem = T % pairs
+    halves = int((bn == 128).sum())
+    assert halves == (2 * rem if 0 < rem and 2 * rem <= pairs else 0) and n == T + halves // 2
+    assert (bn[:n - halves] == 256).all()                        # the halves come last, in pairs of one tile
+    for i in range(n - halves, n, 2):
+        assert m0[i] == m0[i + 1] and n0[i] + 128 == n0[i + 1]
+    if m_tiles >= 8 and n_tiles >= 10 and pairs >= 64:           # the first wave is an 8-row patch, not 2-3 whole rows
+        first = slice(0, pairs)
+        assert len(set(m0[first].tolist())) == 8 and len(set(n0[first].tolist())) <= -(-pairs // 8) + 1
