@@ -184,11 +184,15 @@ def synth_data(rows, d0, n_classes, seed, dtype):
     return x.astype(dtype, copy=False), labels
 
 
-def cpu_reference_run(workload, steps, warmup):
-    """the oracle's faithful single-thread restatement of gradientStep on a bounded sample"""
+def cpu_reference_run(workload, steps, warmup, threads=1, rows=None):
+    """the oracle's restatement of gradientStep on a bounded sample: faithful single-thread loops (threads = 1, the timed
+    CPU baseline), or -- threads > 1, labelled "not the reference" -- the same per-sample arithmetic without the per-sample
+    gradient allocation, the samples of a batch spread over POSIX threads (bit-identical results, tests/test_oracle.py)"""
     from oracle import oracle as orc
     wl = WORKLOADS[workload]
-    dims, rows = wl["dims"], CPU_SAMPLE_ROWS[workload]
+    dims, rows = wl["dims"], rows or CPU_SAMPLE_ROWS[workload]
+    faithful = threads == 1
+    orc.set_threads(threads)
     if wl.get("general"):
         net = orc.OracleNet(dims, kind=orc.NET_GENERAL, inner_act="sigmoid", inner_param=0.0, last_act="sigmoid")
     else:
@@ -205,19 +209,30 @@ def cpu_reference_run(workload, steps, warmup):
     t = np.zeros((x.shape[0], dims[-1]))
     t[np.arange(x.shape[0]), labels] = 1.0
     for s in range(warmup):
-        net.gradient_step(x[s * rows:(s + 1) * rows], t[s * rows:(s + 1) * rows], wl["step"], 0.9, faithful=True)
+        net.gradient_step(x[s * rows:(s + 1) * rows], t[s * rows:(s + 1) * rows], wl["step"], 0.9, faithful=faithful)
     t0 = time.perf_counter()
     for s in range(warmup, warmup + steps):
-        net.gradient_step(x[s * rows:(s + 1) * rows], t[s * rows:(s + 1) * rows], wl["step"], 0.9, faithful=True)
+        net.gradient_step(x[s * rows:(s + 1) * rows], t[s * rows:(s + 1) * rows], wl["step"], 0.9, faithful=faithful)
     dt = time.perf_counter() - t0
+    orc.set_threads(1)
     return rows * steps / dt, dt, rows
 
 
 def cpu_baseline_block(workload):
     cs, cw = CPU_SAMPLE_STEPS[workload]
     val, dt, r = cpu_reference_run(workload, cs, cw)
-    return {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
-            "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" % (cs, r, dt)}
+    blk = {"value": val, "unit": "samples/s", "cores": 1, "kind": "port",
+           "sample": "%d gradient steps of %d samples of the same net by the oracle's faithful loops (%.1f s)" % (cs, r, dt)}
+    if WORKLOADS[workload]["prec"] != "f64":
+        # second line (optional): best-effort CPU on every host core -- NOT the reference, which is serial
+        T = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        if T > 1:
+            v2, dt2, r2 = cpu_reference_run(workload, 2, 1, threads=T, rows=4 * T)
+            blk["all_cores"] = {"value": v2, "unit": "samples/s", "cores": T,
+                                "kind": "port, not the reference (which is serial): the same per-sample arithmetic, the "
+                                        "samples of a batch spread over POSIX threads, no per-sample gradient allocation",
+                                "sample": "2 gradient steps of %d samples (%.1f s)" % (r2, dt2)}
+    return blk
 
 
 def run_reference(args):
