@@ -255,6 +255,15 @@ def run_reference(args):
         "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if wl["prec"] != "f64":
+        # beside it, never instead of it: the threaded port on every host core (not the reference, which is serial)
+        T = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        if T > 1:
+            v2, dt2, r2 = cpu_reference_run(args.workload, 2, 1, threads=T, rows=4 * T)
+            out["cpu_baseline"]["all_cores"] = {
+                "value": v2, "unit": "samples/s", "cores": T, "sample": "2 gradient steps of %d samples (%.1f s)" % (r2, dt2),
+                "kind": "port, not the reference (which is serial): the same per-sample arithmetic, the samples of a batch "
+                        "spread over POSIX threads, no per-sample gradient allocation"}
     emit(out)
 
 
