@@ -156,3 +156,27 @@ def test_tile_order_covers_every_output_once(g, M, N, pairs):
     if m_tiles >= 8 and n_tiles >= 10 and pairs >= 64:           # the first wave is an 8-row patch, not 2-3 whole rows
         first = slice(0, pairs)
         assert len(set(m0[first].tolist())) == 8 and len(set(n0[first].tolist())) <= -(-pairs // 8) + 1
+
+
+def test_reference_arm_contract_line():
+    """`bench.py --impl reference` (the driver's reference arm): rank 0 prints ONE JSON line with the contract's keys, timed on
+    the host by the oracle's faithful loops; every other rank of a torchrun launch exits 0 without output or work."""
+    import json
+    import subprocess
+    import sys
+    cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "c1", "--steps", "3",
+           "--warmup", "3", "--gpus", "2"]
+    env = dict(os.environ, RANK="0", WORLD_SIZE="2", LOCAL_RANK="0")
+    r0 = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert r0.returncode == 0, r0.stderr[-2000:]
+    lines = [l for l in r0.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "train_samples_per_sec" and d["unit"] == "samples/s"
+    assert d["higher_is_better"] is True and d["n_gpus"] == 2 and d["steps"] == 3 and d["warmup"] == 3
+    assert d["value"] > 0 and d["ms_per_step"] > 0 and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["workload"].startswith("c1")
+    r1 = subprocess.run(cmd, env=dict(env, RANK="1", LOCAL_RANK="1"), capture_output=True, text=True, timeout=300)
+    assert r1.returncode == 0 and r1.stdout.strip() == ""
